@@ -1,0 +1,179 @@
+/*
+ * sfm_match.h -- C ABI of the B200 pairwise-matching library (libsfm_match.so).
+ *
+ * This is the drop-in boundary for the `preprocess` hot path of Sovik-Ghosh/SFM.
+ * The reference has no FFI layer (it is pure Python over OpenCV); each entry
+ * point below names the reference call site it replaces (paths relative to the
+ * reference repo root).  Host language above this ABI is Python (ctypes, see
+ * sfm_b200/lib.py and INTEGRATION.md).
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero on failure;
+ *    sfm_last_error(ctx) gives the message.  No C++ exceptions cross the ABI.
+ *  - `d_` pointers are DEVICE memory owned by the caller (PyTorch allocates),
+ *    `h_` pointers are HOST memory owned by the caller.  The library never
+ *    frees caller memory and only keeps the pointers passed to sfm_set_images.
+ *  - `stream` is a cudaStream_t passed as void*; all work is asynchronous on
+ *    that stream; nothing synchronises unless stated.
+ *  - one context per GPU / rank, used from one host thread.
+ */
+#ifndef SFM_MATCH_H_
+#define SFM_MATCH_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SFM_API __attribute__((visibility("default")))
+#else
+#define SFM_API
+#endif
+
+#define SFM_DESC_DIM 128          /* SIFT descriptor length, bytes per row */
+#define SFM_QBLOCK 256            /* query rows per work item of the kNN kernel */
+#define SFM_TTILE 128             /* train rows per tensor-core tile */
+
+typedef struct sfm_ctx sfm_ctx;
+
+/* status codes written per pair by sfm_verify_pairs; they name the reference's
+ * skip gates in ImageMatcher.process_image_pair (utils/find_matches.py:268,
+ * :274, :284, :290). */
+enum {
+    SFM_PAIR_OK = 0,
+    SFM_PAIR_TOO_FEW_FEATURES = 1, /* :268, and Nt<2 (knnMatch rows of length 1 raise at :151) */
+    SFM_PAIR_TOO_FEW_MATCHES = 2,  /* :274  len(matches) < 5 */
+    SFM_PAIR_NO_MODEL = 3,         /* :284  F is None / not 3x3 */
+    SFM_PAIR_QUALITY_FAIL = 4      /* :290  verify_match_quality false */
+};
+
+/* Parameters of RANSAC + verification.  Defaults (sfm_default_params) are the
+ * constants the reference hard-codes. */
+typedef struct sfm_verify_params {
+    double ransac_thresh;   /* 3.0   utils/find_matches.py:282 */
+    double confidence;      /* 0.99  cv2.findFundamentalMat default */
+    int32_t max_iters;      /* 1000  cv2.findFundamentalMat default (rounded up to a multiple of 32) */
+    int32_t min_matches;    /* 5     utils/find_matches.py:274 */
+    uint64_t seed;          /* hypothesis seed; results are a pure function of (seed, pair inputs) */
+    double verify_thresh;   /* 3.0   utils/find_matches.py:157 */
+    int32_t min_inliers;    /* 15    utils/find_matches.py:203 */
+    int32_t lo_iters;       /* 2     inlier-refit rounds on the best hypothesis */
+    double min_ratio;       /* 0.3 */
+    double max_error;       /* 2.0 */
+    double min_spread;      /* 20    utils/find_matches.py:185 */
+} sfm_verify_params;
+
+/* Per-pair metrics, the dict returned by ImageMatcher.geometric_verification
+ * (utils/find_matches.py:190-201) plus RANSAC bookkeeping. */
+typedef struct sfm_pair_metrics {
+    int32_t total_matches;
+    int32_t inliers;             /* sum(inlier_mask) */
+    float inlier_ratio;          /* informative; hosts recompute inliers/total in double */
+    float reprojection_error;    /* mean symmetric error over inliers, +inf if none */
+    float symmetric_error;       /* mean symmetric error over all matches */
+    int32_t well_distributed;    /* 0/1 */
+    int32_t ransac_inliers;      /* support of the best hypothesis under the RANSAC threshold */
+    int32_t ransac_iters;        /* hypotheses evaluated */
+} sfm_pair_metrics;
+
+/* ---- context ---------------------------------------------------------- */
+SFM_API int sfm_create(int device_ordinal, sfm_ctx** out);
+SFM_API void sfm_destroy(sfm_ctx* ctx);
+SFM_API const char* sfm_last_error(sfm_ctx* ctx);     /* ctx may be NULL: last create error */
+SFM_API void sfm_default_params(sfm_verify_params* p);
+SFM_API int sfm_abi_version(void);
+
+/* ---- image set -------------------------------------------------------- */
+/* Register the feature set (replaces the per-pair detect_features calls,
+ * utils/find_matches.py:265-266; extraction itself stays on the host).
+ *   d_desc     u8  [total_rows, 128] packed row-major, 16-byte aligned
+ *   d_kps      f32 [total_rows, 2]   keypoint (x, y) per descriptor row; may be NULL
+ *                                     if sfm_verify_pairs is not used
+ *   h_offsets  i64 [n_images + 1]    row range of image i is [off[i], off[i+1])
+ * Launches the descriptor-norm kernel on `stream`.  The pointers must stay
+ * valid until the next sfm_set_images / sfm_destroy. */
+SFM_API int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
+                   const int64_t* h_offsets, int32_t n_images, void* stream);
+
+/* ---- K1: brute-force L2 kNN, k = 2 ------------------------------------ */
+/* Replaces cv2.BFMatcher(NORM_L2).knnMatch(desc1, desc2, k=2)
+ * (utils/find_matches.py:144-147, L2 per SURVEY.md 0.2) for a batch of
+ * DIRECTED pairs (query image, train image).
+ *   h_pairs    i32 [n_pairs, 2]
+ *   h_row_off  i64 [n_pairs + 1]  first output row of pair p; pair p owns
+ *                                  n_query(p) consecutive rows
+ *   d_knn      i32 [total_rows, 4] per query row: (idx1, idx2, d1^2, d2^2),
+ *              exact integers, ascending distance, lowest train index wins
+ *              ties; idx2 = -1 and d2^2 = INT32_MAX when the train image has
+ *              fewer than 2 rows (idx1 too when it has none). */
+SFM_API int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
+             const int64_t* h_row_off, int32_t* d_knn, void* stream);
+
+/* ---- K2: ratio test (+ mutual-NN) and order-preserving compaction ------ */
+/* Replaces the ratio loop utils/find_matches.py:150-153: keep a query row iff
+ * float64(f32sqrt(d1^2)) < ratio * float64(f32sqrt(d2^2)); with d_knn_rev
+ * non-NULL additionally iff the best train row's own nearest query row
+ * (d_knn_rev, computed by sfm_knn2 on the reversed pairs with offsets
+ * h_row_off_rev) is this query row (README.md:108; == BFMatcher crossCheck).
+ * Output arena uses the forward row offsets: pair p may write up to
+ * n_query(p) matches starting at h_row_off[p], ascending queryIdx:
+ *   d_mq, d_mt  i32 query / train row index within their image
+ *   d_md2       i32 squared distance of the kept match
+ *   d_count     i32 [n_pairs] */
+SFM_API int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
+                       const int64_t* h_row_off, const int32_t* d_knn,
+                       const int64_t* h_row_off_rev, const int32_t* d_knn_rev,
+                       double ratio, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2,
+                       int32_t* d_count, void* stream);
+
+/* ---- K3 + K4: RANSAC fundamental matrix + geometric verification ------ */
+/* Replaces, per pair: the point gather utils/find_matches.py:278-279,
+ * cv2.findFundamentalMat(pts1, pts2, FM_RANSAC, 3.0) (:282),
+ * geometric_verification (:157-201) and verify_match_quality (:203-214).
+ * Inputs are the arenas written by sfm_filter_matches.  Outputs:
+ *   d_pts1, d_pts2  f32 [arena, 2]  gathered keypoints (rows of pair p at h_row_off[p])
+ *   d_F             f64 [n_pairs, 9] row-major, rank 2, F[2][2] = 1 when not tiny
+ *   d_mask          u8  [arena]     inlier_mask of geometric_verification
+ *   d_sym           f32 [arena]     symmetric_errors
+ *   d_metrics       [n_pairs], d_status i32 [n_pairs] (SFM_PAIR_*) */
+SFM_API int sfm_verify_pairs(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
+                     const int64_t* h_row_off, const int32_t* d_mq, const int32_t* d_mt,
+                     const int32_t* d_count, const sfm_verify_params* params,
+                     float* d_pts1, float* d_pts2, double* d_F, uint8_t* d_mask,
+                     float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
+                     void* stream);
+
+/* geometric_verification alone for a caller-supplied F (parity tests of
+ * utils/find_matches.py:157-214 against the golden fundamental/*.npz):
+ *   h_off i64 [n_pairs+1] point ranges, d_pts1/d_pts2 f32 [total,2], d_F f64 [n_pairs,9] */
+SFM_API int sfm_verify_given_F(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off,
+                       const float* d_pts1, const float* d_pts2, const double* d_F,
+                       const sfm_verify_params* params, uint8_t* d_mask, float* d_sym,
+                       sfm_pair_metrics* d_metrics, int32_t* d_status, void* stream);
+
+/* RANSAC + verification on caller-supplied correspondences (no gather):
+ * same outputs as sfm_verify_pairs. */
+SFM_API int sfm_ransac_points(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off,
+                      const float* d_pts1, const float* d_pts2,
+                      const sfm_verify_params* params, double* d_F, uint8_t* d_mask,
+                      float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
+                      void* stream);
+
+/* ---- measurement helpers ---------------------------------------------- */
+/* Number of kernel launches issued by this context since creation. */
+SFM_API int64_t sfm_launch_count(sfm_ctx* ctx);
+/* Tensor-pipe peak probe: runs an MMA-only tcgen05 kind::i8 loop on every SM
+ * for `iters` 128x128x128 tile products per CTA and returns the elapsed
+ * milliseconds (CUDA events) in *ms and the int8 op count in *ops. */
+SFM_API int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream);
+/* Debug: raw u8 x u8 dot products of one 128x128 tile pair through the same
+ * TMA + tcgen05 path (rows q_row.. of the registered set against t_row..),
+ * written to d_out i32 [128,128]. */
+SFM_API int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFM_MATCH_H_ */

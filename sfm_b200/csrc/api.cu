@@ -1,0 +1,427 @@
+// C ABI of libsfm_match.so (see include/sfm_match.h): context, metadata
+// staging and kernel sequencing.  No torch types; device memory that crosses
+// the boundary is owned by the caller.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace {
+
+std::string g_create_error;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        const size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&p), want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct sfm_ctx {
+    int device = 0;
+    int num_sms = 0;
+    std::string err;
+    int64_t launches = 0;
+    EncodeTiledFn encode = nullptr;
+
+    // registered image set
+    const uint8_t* d_desc = nullptr;
+    const float* d_kps = nullptr;
+    int32_t n_images = 0;
+    int64_t total_rows = 0;
+    int64_t pad_total = 0;
+    std::vector<int64_t> h_off, h_pad;
+    CUtensorMap tmap;
+    bool have_tmap = false;
+    DevBuf<int64_t> d_img_off, d_pad_off;
+    DevBuf<int32_t> d_norms, d_norms_pad;
+
+    // per-call metadata scratch
+    DevBuf<int32_t> d_pairs;
+    DevBuf<int64_t> d_meta;      // blk_prefix | row_off | row_off_rev
+    DevBuf<sfm::WorkItem> d_work;
+    std::vector<int64_t> h_meta;
+
+    int fail(const char* fmt, ...) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        err = buf;
+        return 1;
+    }
+};
+
+#define SFM_CUDA(ctx, call)                                                                      \
+    do {                                                                                         \
+        cudaError_t e__ = (call);                                                                \
+        if (e__ != cudaSuccess)                                                                  \
+            return (ctx)->fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                               __LINE__);                                                        \
+    } while (0)
+
+namespace {
+
+int check_pairs(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs) {
+    if (n_pairs < 0) return ctx->fail("n_pairs < 0");
+    if (n_pairs > 0 && !h_pairs) return ctx->fail("h_pairs is NULL");
+    for (int32_t p = 0; p < n_pairs; ++p) {
+        const int32_t a = h_pairs[2 * p], b = h_pairs[2 * p + 1];
+        if (a < 0 || b < 0 || a >= ctx->n_images || b >= ctx->n_images)
+            return ctx->fail("pair %d = (%d, %d) out of range for %d images", p, a, b, ctx->n_images);
+    }
+    return 0;
+}
+
+// Copy the pair list and up to three i64 arrays of n_pairs+1 entries to the device.
+int stage_meta(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* a,
+               const int64_t* b, const int64_t* c, cudaStream_t st, const int64_t** da,
+               const int64_t** db, const int64_t** dc) {
+    const size_t n1 = static_cast<size_t>(n_pairs) + 1;
+    SFM_CUDA(ctx, ctx->d_pairs.reserve(static_cast<size_t>(n_pairs) * 2 + 2));
+    SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
+    if (n_pairs > 0)
+        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_pairs.p, h_pairs, sizeof(int32_t) * 2 * n_pairs,
+                                      cudaMemcpyHostToDevice, st));
+    const int64_t* src[3] = {a, b, c};
+    const int64_t** dst[3] = {da, db, dc};
+    for (int i = 0; i < 3; ++i) {
+        if (!dst[i]) continue;
+        *dst[i] = nullptr;
+        if (!src[i]) continue;
+        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p + i * n1, src[i], sizeof(int64_t) * n1,
+                                      cudaMemcpyHostToDevice, st));
+        *dst[i] = ctx->d_meta.p + i * n1;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sfm_abi_version(void) { return 1; }
+
+void sfm_default_params(sfm_verify_params* p) {
+    if (!p) return;
+    p->ransac_thresh = 3.0;
+    p->confidence = 0.99;
+    p->max_iters = 1000;
+    p->min_matches = 5;
+    p->seed = 0x5F3759DF2024ull;
+    p->verify_thresh = 3.0;
+    p->min_inliers = 15;
+    p->lo_iters = 2;
+    p->min_ratio = 0.3;
+    p->max_error = 2.0;
+    p->min_spread = 20.0;
+}
+
+const char* sfm_last_error(sfm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int sfm_create(int device_ordinal, sfm_ctx** out) {
+    if (!out) return 1;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+        return 1;
+    }
+    if (device_ordinal < 0 || device_ordinal >= n) {
+        g_create_error = "device ordinal out of range";
+        return 1;
+    }
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device_ordinal);
+    if (e != cudaSuccess) {
+        g_create_error = cudaGetErrorString(e);
+        return 1;
+    }
+    if (prop.major != 10) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "device %d is sm_%d%d; this library is sm_100a only (tcgen05/TMEM)",
+                 device_ordinal, prop.major, prop.minor);
+        g_create_error = buf;
+        return 1;
+    }
+    e = cudaSetDevice(device_ordinal);
+    if (e != cudaSuccess) {
+        g_create_error = cudaGetErrorString(e);
+        return 1;
+    }
+    sfm_ctx* ctx = new sfm_ctx();
+    ctx->device = device_ordinal;
+    ctx->num_sms = prop.multiProcessorCount;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+        g_create_error = "cuTensorMapEncodeTiled not available from the driver";
+        delete ctx;
+        return 1;
+    }
+    ctx->encode = reinterpret_cast<EncodeTiledFn>(fn);
+    *out = ctx;
+    return 0;
+}
+
+void sfm_destroy(sfm_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    ctx->d_img_off.release();
+    ctx->d_pad_off.release();
+    ctx->d_norms.release();
+    ctx->d_norms_pad.release();
+    ctx->d_pairs.release();
+    ctx->d_meta.release();
+    ctx->d_work.release();
+    delete ctx;
+}
+
+int64_t sfm_launch_count(sfm_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
+                   const int64_t* h_offsets, int32_t n_images, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_images < 0 || !h_offsets) return ctx->fail("bad image set arguments");
+    if (h_offsets[0] != 0) return ctx->fail("h_offsets[0] must be 0");
+    for (int i = 0; i < n_images; ++i)
+        if (h_offsets[i + 1] < h_offsets[i]) return ctx->fail("h_offsets must be non-decreasing");
+    const int64_t total = h_offsets[n_images];
+    if (total >= (int64_t(1) << 31) - 512) return ctx->fail("too many descriptor rows");
+    if (total > 0 && !d_desc) return ctx->fail("d_desc is NULL");
+    if (reinterpret_cast<uintptr_t>(d_desc) & 15) return ctx->fail("d_desc must be 16-byte aligned");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    ctx->d_desc = d_desc;
+    ctx->d_kps = d_kps;
+    ctx->n_images = n_images;
+    ctx->total_rows = total;
+    ctx->h_off.assign(h_offsets, h_offsets + n_images + 1);
+    ctx->h_pad.resize(n_images + 1);
+    ctx->h_pad[0] = 0;
+    for (int i = 0; i < n_images; ++i) {
+        const int64_t n = h_offsets[i + 1] - h_offsets[i];
+        ctx->h_pad[i + 1] = ctx->h_pad[i] + (n + SFM_TTILE - 1) / SFM_TTILE * SFM_TTILE;
+    }
+    ctx->pad_total = ctx->h_pad[n_images];
+    if (ctx->pad_total >= (int64_t(1) << 31)) return ctx->fail("padded column space too large");
+
+    SFM_CUDA(ctx, ctx->d_img_off.reserve(n_images + 1));
+    SFM_CUDA(ctx, ctx->d_pad_off.reserve(n_images + 1));
+    SFM_CUDA(ctx, ctx->d_norms.reserve(static_cast<size_t>(total) + 1));
+    SFM_CUDA(ctx, ctx->d_norms_pad.reserve(static_cast<size_t>(ctx->pad_total) + 4));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
+                                  cudaMemcpyHostToDevice, st));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_pad_off.p, ctx->h_pad.data(), sizeof(int64_t) * (n_images + 1),
+                                  cudaMemcpyHostToDevice, st));
+
+    ctx->have_tmap = false;
+    if (total > 0) {
+        const cuuint64_t gdim[2] = {SFM_DESC_DIM, static_cast<cuuint64_t>(total)};
+        const cuuint64_t gstride[1] = {SFM_DESC_DIM};
+        const cuuint32_t box[2] = {SFM_DESC_DIM, SFM_TTILE};
+        const cuuint32_t estr[2] = {1, 1};
+        CUresult r = ctx->encode(&ctx->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                                 const_cast<uint8_t*>(d_desc), gdim, gstride, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled failed: CUresult %d", int(r));
+        ctx->have_tmap = true;
+    }
+    sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, n_images, ctx->pad_total,
+                      ctx->d_norms.p, ctx->d_norms_pad.p, st, &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    return 0;
+}
+
+int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
+             int32_t* d_knn, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
+    if (n_pairs == 0) return 0;
+    if (!h_row_off || !d_knn) return ctx->fail("NULL argument");
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered (sfm_set_images)");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    // work-item prefix: ceil(n_query / 256) blocks per pair
+    ctx->h_meta.resize(static_cast<size_t>(n_pairs) + 1);
+    ctx->h_meta[0] = 0;
+    for (int32_t p = 0; p < n_pairs; ++p) {
+        const int32_t qi = h_pairs[2 * p];
+        const int64_t nq = ctx->h_off[qi + 1] - ctx->h_off[qi];
+        if (h_row_off[p + 1] - h_row_off[p] < nq)
+            return ctx->fail("h_row_off leaves pair %d fewer than its %lld query rows", p, (long long)nq);
+        ctx->h_meta[p + 1] = ctx->h_meta[p] + (nq + SFM_QBLOCK - 1) / SFM_QBLOCK;
+    }
+    const int64_t n_work = ctx->h_meta[n_pairs];
+    const int64_t *d_prefix, *d_row;
+    if (stage_meta(ctx, h_pairs, n_pairs, ctx->h_meta.data(), h_row_off, nullptr, st, &d_prefix, &d_row,
+                   nullptr))
+        return 1;
+    SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
+    sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
+                           ctx->d_work.p, st, &ctx->launches);
+    int r = sfm::launch_knn2(ctx->tmap, ctx->d_work.p, n_work, ctx->d_norms.p, ctx->d_norms_pad.p, d_knn,
+                             ctx->num_sms, st, &ctx->launches);
+    if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
+                       const int64_t* h_row_off, const int32_t* d_knn, const int64_t* h_row_off_rev,
+                       const int32_t* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,
+                       int32_t* d_md2, int32_t* d_count, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
+    if (n_pairs == 0) return 0;
+    if (!h_row_off || !d_knn || !d_mq || !d_mt || !d_md2 || !d_count) return ctx->fail("NULL argument");
+    if ((d_knn_rev != nullptr) != (h_row_off_rev != nullptr))
+        return ctx->fail("d_knn_rev and h_row_off_rev must be given together");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t *d_row, *d_row_rev;
+    if (stage_meta(ctx, h_pairs, n_pairs, nullptr, h_row_off, h_row_off_rev, st, nullptr, &d_row,
+                   &d_row_rev))
+        return 1;
+    sfm::launch_filter(ctx->d_pairs.p, n_pairs, ctx->d_img_off.p, d_row,
+                       reinterpret_cast<const int4*>(d_knn), d_row_rev,
+                       reinterpret_cast<const int4*>(d_knn_rev), ratio, d_mq, d_mt, d_md2, d_count, st,
+                       &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    return 0;
+}
+
+int sfm_verify_pairs(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
+                     const int32_t* d_mq, const int32_t* d_mt, const int32_t* d_count,
+                     const sfm_verify_params* params, float* d_pts1, float* d_pts2, double* d_F,
+                     uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
+                     void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
+    if (n_pairs == 0) return 0;
+    if (!h_row_off || !d_mq || !d_mt || !d_count || !d_pts1 || !d_pts2 || !d_F || !d_mask || !d_sym ||
+        !d_metrics || !d_status)
+        return ctx->fail("NULL argument");
+    if (!ctx->d_kps) return ctx->fail("no keypoints registered (sfm_set_images d_kps)");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    sfm_verify_params prm;
+    if (params) prm = *params; else sfm_default_params(&prm);
+    const int64_t* d_row;
+    if (stage_meta(ctx, h_pairs, n_pairs, nullptr, h_row_off, nullptr, st, nullptr, &d_row, nullptr))
+        return 1;
+    sfm::launch_gather_points(ctx->d_pairs.p, n_pairs, ctx->d_img_off.p, d_row, d_mq, d_mt, d_count,
+                              ctx->d_kps, d_pts1, d_pts2, st, &ctx->launches);
+    int r = sfm::launch_ransac_verify(n_pairs, d_row, d_count, ctx->d_pairs.p, d_pts1, d_pts2, nullptr,
+                                      prm, d_F, d_mask, d_sym, d_metrics, d_status, st, &ctx->launches);
+    if (r) return ctx->fail("ransac launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+static int points_entry(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off, const float* d_pts1,
+                        const float* d_pts2, const double* d_F_in, const sfm_verify_params* params,
+                        double* d_F, uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics,
+                        int32_t* d_status, cudaStream_t st) {
+    if (n_pairs < 0) return ctx->fail("n_pairs < 0");
+    if (n_pairs == 0) return 0;
+    if (!h_off || !d_pts1 || !d_pts2 || !d_mask || !d_sym || !d_metrics || !d_status)
+        return ctx->fail("NULL argument");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    sfm_verify_params prm;
+    if (params) prm = *params; else sfm_default_params(&prm);
+    const size_t n1 = static_cast<size_t>(n_pairs) + 1;
+    SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p, h_off, sizeof(int64_t) * n1, cudaMemcpyHostToDevice, st));
+    int r = sfm::launch_ransac_verify(n_pairs, ctx->d_meta.p, nullptr, nullptr, d_pts1, d_pts2, d_F_in, prm,
+                                      d_F, d_mask, d_sym, d_metrics, d_status, st, &ctx->launches);
+    if (r) return ctx->fail("ransac launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_verify_given_F(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off, const float* d_pts1,
+                       const float* d_pts2, const double* d_F, const sfm_verify_params* params,
+                       uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
+                       void* stream) {
+    if (!ctx) return 1;
+    if (!d_F && n_pairs > 0) return ctx->fail("d_F is NULL");
+    return points_entry(ctx, n_pairs, h_off, d_pts1, d_pts2, d_F, params, nullptr, d_mask, d_sym,
+                        d_metrics, d_status, static_cast<cudaStream_t>(stream));
+}
+
+int sfm_ransac_points(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off, const float* d_pts1,
+                      const float* d_pts2, const sfm_verify_params* params, double* d_F,
+                      uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
+                      void* stream) {
+    if (!ctx) return 1;
+    if (!d_F && n_pairs > 0) return ctx->fail("d_F is NULL");
+    return points_entry(ctx, n_pairs, h_off, d_pts1, d_pts2, nullptr, params, d_F, d_mask, d_sym,
+                        d_metrics, d_status, static_cast<cudaStream_t>(stream));
+}
+
+int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream) {
+    if (!ctx) return 1;
+    if (iters <= 0 || !ms || !ops) return ctx->fail("bad probe arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1;
+    SFM_CUDA(ctx, cudaEventCreate(&e0));
+    SFM_CUDA(ctx, cudaEventCreate(&e1));
+    int r = sfm::launch_mma_probe(iters, ctx->num_sms, st, &ctx->launches);   // warm-up
+    if (!r) {
+        cudaEventRecord(e0, st);
+        r = sfm::launch_mma_probe(iters, ctx->num_sms, st, &ctx->launches);
+        cudaEventRecord(e1, st);
+    }
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (r || e != cudaSuccess) {
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        return ctx->fail("probe failed: %s", cudaGetErrorString(r ? static_cast<cudaError_t>(r) : e));
+    }
+    cudaEventElapsedTime(ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ops = 2.0 * 128.0 * 256.0 * 128.0 * static_cast<double>(iters) * ctx->num_sms;
+    return 0;
+}
+
+int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream) {
+    if (!ctx) return 1;
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
+    if (!d_out) return ctx->fail("d_out is NULL");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    int r = sfm::launch_debug_dot(ctx->tmap, static_cast<int32_t>(q_row), static_cast<int32_t>(t_row),
+                                  d_out, static_cast<cudaStream_t>(stream), &ctx->launches);
+    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,96 @@
+// K2: Lowe ratio test (+ optional mutual-NN check) and order-preserving
+// compaction of the surviving matches.
+//
+// Replaces the Python loop of reference utils/find_matches.py:150-153
+//     for m, n in matches: if m.distance < 0.75 * n.distance: good.append(m)
+// where m.distance / n.distance are float32 square roots of the exact integer
+// squared distances and the comparison is evaluated in double precision; that
+// rule is reproduced bit for bit (correctly rounded f32 sqrt, widened, one
+// double multiply).  Mutual-NN (README.md:108, == BFMatcher crossCheck=True):
+// the best train row's own nearest query row must be this query row.
+//
+// HBM-bound integer pass: one CTA per pair streams 16 B per query row with
+// 128-bit loads and writes <= 12 B per kept match; a block-wide ballot scan
+// keeps ascending queryIdx order.
+#include "kernels.h"
+
+namespace sfm {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ bool ratio_pass(int d1, int d2, double ratio) {
+    const float s1 = __fsqrt_rn(static_cast<float>(d1));   // exact ints < 2^24 -> exact floats
+    const float s2 = __fsqrt_rn(static_cast<float>(d2));
+    return static_cast<double>(s1) < ratio * static_cast<double>(s2);
+}
+
+__global__ void __launch_bounds__(kThreads)
+filter_kernel(const int32_t* __restrict__ pairs, int n_pairs, const long long* __restrict__ img_off,
+              const long long* __restrict__ row_off, const int4* __restrict__ knn,
+              const long long* __restrict__ row_off_rev, const int4* __restrict__ knn_rev,
+              double ratio, int32_t* __restrict__ mq, int32_t* __restrict__ mt,
+              int32_t* __restrict__ md2, int32_t* __restrict__ count) {
+    __shared__ int warp_tot[kThreads / 32];
+    __shared__ int base_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+        const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
+        const int nq = static_cast<int>(img_off[qi + 1] - img_off[qi]);
+        const int nt = static_cast<int>(img_off[ti + 1] - img_off[ti]);
+        const long long r0 = row_off[p];
+        const int4* rev = knn_rev ? knn_rev + row_off_rev[p] : nullptr;
+        if (threadIdx.x == 0) base_s = 0;
+        __syncthreads();
+        for (int q0 = 0; q0 < nq; q0 += kThreads) {
+            const int q = q0 + threadIdx.x;
+            bool keep = false;
+            int4 r = make_int4(-1, -1, 0, 0);
+            if (q < nq && nt >= 2) {
+                r = __ldg(knn + r0 + q);
+                keep = r.x >= 0 && r.y >= 0 && ratio_pass(r.z, r.w, ratio);
+                if (keep && rev) keep = __ldg(&rev[r.x].x) == q;
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) warp_tot[warp] = __popc(bal);
+            __syncthreads();
+            int before = base_s, total = 0;
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; ++w) {
+                const int c = warp_tot[w];
+                if (w < warp) before += c;
+                total += c;
+            }
+            if (keep) {
+                const long long o = r0 + before + __popc(bal & ((1u << lane) - 1u));
+                mq[o] = q;
+                mt[o] = r.x;
+                md2[o] = r.z;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) base_s += total;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) count[p] = base_s;
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
+                   const int64_t* d_row_off, const int4* d_knn, const int64_t* d_row_off_rev,
+                   const int4* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,
+                   int32_t* d_md2, int32_t* d_count, cudaStream_t st, int64_t* launches) {
+    if (n_pairs <= 0) return;
+    const int grid = n_pairs < 148 * 8 ? n_pairs : 148 * 8;
+    filter_kernel<<<grid, kThreads, 0, st>>>(
+        d_pairs, n_pairs, reinterpret_cast<const long long*>(d_img_off),
+        reinterpret_cast<const long long*>(d_row_off), d_knn,
+        reinterpret_cast<const long long*>(d_row_off_rev), d_knn_rev, ratio, d_mq, d_mt, d_md2,
+        d_count);
+    ++*launches;
+}
+
+}  // namespace sfm

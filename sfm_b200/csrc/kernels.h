@@ -1,0 +1,58 @@
+// Internal launch interface between api.cu and the kernel translation units.
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "../../include/sfm_match.h"
+
+namespace sfm {
+
+// One unit of kNN work: a block of up to SFM_QBLOCK query rows of one image
+// against every row of one train image.
+struct __align__(16) WorkItem {
+    int32_t q_row;    // first query row (row index into the packed descriptor array)
+    int32_t q_cnt;    // valid query rows in this block (1..256)
+    int32_t t_row;    // first row of the train image
+    int32_t t_cnt;    // rows of the train image
+    int32_t t_pad;    // offset of the train image in the 128-padded column-norm array
+    int32_t reserved;
+    int64_t out_row;  // first output row of this block in d_knn
+};
+static_assert(sizeof(WorkItem) == 32, "WorkItem must be 32 bytes");
+
+// ---- norms.cu / knn.cu
+void launch_norms(const uint8_t* d_desc, int64_t total_rows, const int64_t* d_img_off,
+                  const int64_t* d_pad_off, int32_t n_images, int64_t pad_total, int32_t* d_norms,
+                  int32_t* d_norms_pad, cudaStream_t st, int64_t* launches);
+void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_blk_prefix,
+                       const int64_t* d_row_off, const int64_t* d_img_off, const int64_t* d_pad_off,
+                       WorkItem* d_work, cudaStream_t st, int64_t* launches);
+int launch_knn2(const CUtensorMap& tmap, const WorkItem* d_work, int64_t n_work,
+                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_knn, int num_sms,
+                cudaStream_t st, int64_t* launches);
+int launch_debug_dot(const CUtensorMap& tmap, int32_t q_row, int32_t t_row, int32_t* d_out,
+                     cudaStream_t st, int64_t* launches);
+int launch_mma_probe(int32_t iters, int num_sms, cudaStream_t st, int64_t* launches);
+
+// ---- filter.cu
+void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
+                   const int64_t* d_row_off, const int4* d_knn, const int64_t* d_row_off_rev,
+                   const int4* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,
+                   int32_t* d_md2, int32_t* d_count, cudaStream_t st, int64_t* launches);
+
+// ---- ransac.cu
+void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
+                          const int64_t* d_row_off, const int32_t* d_mq, const int32_t* d_mt,
+                          const int32_t* d_count, const float* d_kps, float* d_pts1, float* d_pts2,
+                          cudaStream_t st, int64_t* launches);
+// d_cnt may be NULL: then the count of pair p is d_off[p+1]-d_off[p].
+// d_F_in non-NULL: skip RANSAC and verify against the supplied F.
+// d_pair_ids (nullable) i32 [n_pairs,2]: image ids keying the hypothesis RNG.
+int launch_ransac_verify(int32_t n_pairs, const int64_t* d_off, const int32_t* d_cnt,
+                         const int32_t* d_pair_ids, const float* d_pts1, const float* d_pts2, const double* d_F_in,
+                         const sfm_verify_params& prm, double* d_F, uint8_t* d_mask, float* d_sym,
+                         sfm_pair_metrics* d_metrics, int32_t* d_status, cudaStream_t st,
+                         int64_t* launches);
+
+}  // namespace sfm

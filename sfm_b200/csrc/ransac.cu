@@ -1,0 +1,454 @@
+// K3 + K4: batched RANSAC fundamental matrix and geometric verification.
+//
+// Replaces, per image pair (reference utils/find_matches.py):
+//   :278-279  point gather from the keypoints
+//   :282      cv2.findFundamentalMat(pts1, pts2, cv2.FM_RANSAC, 3.0)
+//   :157-201  ImageMatcher.geometric_verification
+//   :203-214  ImageMatcher.verify_match_quality
+//
+// One CTA per pair.  Correspondences are staged in shared memory (SoA float4
+// per match, 2048 at a time); every warp owns a batch of 32 hypotheses, one
+// per lane: the lane draws its 8-sample with a counter-based RNG, solves the
+// normalised 8-point system in registers and then walks the staged points
+// (shared-memory broadcast reads) counting Sampson inliers.  After each round
+// of 8 x 32 hypotheses the block keeps the best model and re-evaluates the
+// adaptive stopping rule.  The best model is polished by least-squares refits
+// on its inliers (float64 normal equations, block-reduced), and the final F is
+// pushed through the reference's verification arithmetic: epilines in float64
+// rounded to float32 exactly as cv2.computeCorrespondEpilines does, then the
+// reference's float32 NumPy expressions without FMA contraction, so that for
+// an identical F the inlier mask is bit-identical to the reference's.
+#include <cfloat>
+
+#include "kernels.h"
+#include "ransac_core.h"
+
+namespace sfm {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kChunk = 2048;   // staged correspondences per pass (32 KiB)
+constexpr int kMinSample = 8;
+
+struct Shared {
+    float4 pts[kChunk];
+    double red[kWarps][48];
+    double res[48];
+    double Fd[9];
+    float bestF[9];
+    float warpF[kWarps][9];
+    int warp_cnt[kWarps];
+    float warp_cost[kWarps];
+    int warp_hyp[kWarps];
+    int best_cnt;
+    float best_cost;
+    int need;
+    int flag;
+};
+
+template <int N>
+__device__ void block_sum(double (&v)[N], Shared& sh) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        double x = v[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) sh.red[warp][i] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < N) {
+        double s = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) s += sh.red[w][threadIdx.x];
+        sh.res[threadIdx.x] = s;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = sh.res[i];
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 load_match(const float* __restrict__ p1,
+                                             const float* __restrict__ p2, long long i) {
+    const float2 a = __ldg(reinterpret_cast<const float2*>(p1) + i);
+    const float2 b = __ldg(reinterpret_cast<const float2*>(p2) + i);
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+
+// The reference's symmetric epipolar error of one correspondence, bit for bit
+// (oracle/fundamental.py::_epilines + _verification_from_lines).
+__device__ __forceinline__ float symmetric_error(const double (&F)[9], float x1, float y1, float x2,
+                                                 float y2) {
+    auto line = [](double f0, double f1, double f2, double f3, double f4, double f5, double f6,
+                   double f7, double f8, float x, float y, float& la, float& lb, float& lc) {
+        const double xd = x, yd = y;
+        const double a = __dadd_rn(__dadd_rn(__dmul_rn(f0, xd), __dmul_rn(f1, yd)), f2);
+        const double b = __dadd_rn(__dadd_rn(__dmul_rn(f3, xd), __dmul_rn(f4, yd)), f5);
+        const double c = __dadd_rn(__dadd_rn(__dmul_rn(f6, xd), __dmul_rn(f7, yd)), f8);
+        double nu = __dadd_rn(__dmul_rn(a, a), __dmul_rn(b, b));
+        nu = nu != 0.0 ? __ddiv_rn(1.0, __dsqrt_rn(nu)) : 1.0;
+        la = static_cast<float>(__dmul_rn(a, nu));
+        lb = static_cast<float>(__dmul_rn(b, nu));
+        lc = static_cast<float>(__dmul_rn(c, nu));
+    };
+    float a1, b1, c1, a2, b2, c2;
+    // lines1: epilines in image 1 of the image-2 points, F^T x2   (:160)
+    line(F[0], F[3], F[6], F[1], F[4], F[7], F[2], F[5], F[8], x2, y2, a1, b1, c1);
+    // lines2: epilines in image 2 of the image-1 points, F x1     (:162)
+    line(F[0], F[1], F[2], F[3], F[4], F[5], F[6], F[7], F[8], x1, y1, a2, b2, c2);
+    const float e1 = __fdiv_rn(fabsf(__fadd_rn(__fadd_rn(__fmul_rn(x1, a1), __fmul_rn(y1, b1)), c1)),
+                               __fsqrt_rn(__fadd_rn(__fmul_rn(a1, a1), __fmul_rn(b1, b1))));
+    const float e2 = __fdiv_rn(fabsf(__fadd_rn(__fadd_rn(__fmul_rn(x2, a2), __fmul_rn(y2, b2)), c2)),
+                               __fsqrt_rn(__fadd_rn(__fmul_rn(a2, a2), __fmul_rn(b2, b2))));
+    return __fmul_rn(__fadd_rn(e1, e2), 0.5f);
+}
+
+__device__ void write_skip(int p, int m, int status, double* F_out, sfm_pair_metrics* metrics,
+                           int32_t* status_out) {
+    if (threadIdx.x < 9 && F_out) F_out[9ll * p + threadIdx.x] = 0.0;
+    if (threadIdx.x == 0) {
+        sfm_pair_metrics mt;
+        mt.total_matches = m;
+        mt.inliers = 0;
+        mt.inlier_ratio = 0.f;
+        mt.reprojection_error = __int_as_float(0x7f800000);
+        mt.symmetric_error = 0.f;
+        mt.well_distributed = 0;
+        mt.ransac_inliers = 0;
+        mt.ransac_iters = 0;
+        metrics[p] = mt;
+        status_out[p] = status;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32_t* __restrict__ cnt,
+                     const int32_t* __restrict__ pair_ids, const float* __restrict__ pts1,
+                     const float* __restrict__ pts2, const double* __restrict__ F_in,
+                     sfm_verify_params prm, double* __restrict__ F_out, uint8_t* __restrict__ mask,
+                     float* __restrict__ sym, sfm_pair_metrics* __restrict__ metrics,
+                     int32_t* __restrict__ status_out) {
+    __shared__ Shared sh;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float thr2 = static_cast<float>(prm.ransac_thresh * prm.ransac_thresh);
+    const int max_iters = (prm.max_iters + 31) & ~31;
+
+    for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+        __syncthreads();
+        const long long base = off[p];
+        const int m = cnt ? cnt[p] : static_cast<int>(off[p + 1] - base);
+        const float* p1 = pts1 + 2 * base;
+        const float* p2 = pts2 + 2 * base;
+        int ransac_inl = 0, ransac_it = 0;
+
+        if (F_in) {
+            if (threadIdx.x < 9) sh.Fd[threadIdx.x] = F_in[9ll * p + threadIdx.x];
+            __syncthreads();
+        } else {
+            if (m < prm.min_matches) {
+                write_skip(p, m, SFM_PAIR_TOO_FEW_MATCHES, F_out, metrics, status_out);
+                continue;
+            }
+            if (m < kMinSample) {
+                write_skip(p, m, SFM_PAIR_NO_MODEL, F_out, metrics, status_out);
+                continue;
+            }
+            const uint64_t key = pair_ids ? rc::pair_key(prm.seed, pair_ids[2 * p], pair_ids[2 * p + 1])
+                                          : rc::pair_key(prm.seed, static_cast<uint32_t>(p), 0xffffffffu);
+            if (threadIdx.x == 0) {
+                sh.best_cnt = -1;
+                sh.best_cost = FLT_MAX;
+                sh.need = max_iters;
+            }
+            const bool resident = m <= kChunk;
+            if (resident)
+                for (int i = threadIdx.x; i < m; i += kThreads) sh.pts[i] = load_match(p1, p2, i);
+            __syncthreads();
+
+            // ------------------------------------------------ hypothesis rounds
+            int done = 0;
+            while (done < sh.need) {
+                const int hyp = done + warp * 32 + lane;
+                float F[9];
+                bool ok = false;
+                if (hyp < max_iters) {
+                    uint32_t idx[8];
+                    rc::sample8(key, hyp, m, idx);
+                    float s[8][4];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 q = load_match(p1, p2, idx[j]);
+                        s[j][0] = q.x; s[j][1] = q.y; s[j][2] = q.z; s[j][3] = q.w;
+                    }
+                    ok = rc::solve8(s, F);
+                }
+                int c = 0;
+                float cost = 0.f;
+                for (int c0 = 0; c0 < m; c0 += kChunk) {
+                    const int n = min(kChunk, m - c0);
+                    if (!resident) {
+                        __syncthreads();
+                        for (int i = threadIdx.x; i < n; i += kThreads)
+                            sh.pts[i] = load_match(p1, p2, c0 + i);
+                        __syncthreads();
+                    }
+                    if (ok) {
+#pragma unroll 4
+                        for (int i = 0; i < n; ++i) {
+                            const float4 q = sh.pts[i];
+                            const float e = rc::sampson_sq<float>(F, q.x, q.y, q.z, q.w);
+                            c += e < thr2;
+                            cost += fminf(e, thr2);
+                        }
+                    }
+                }
+                if (!ok) { c = -1; cost = FLT_MAX; }
+                // warp arg-best: more inliers, then lower truncated cost, then lower id
+                int bc = c, bh = hyp;
+                float bcost = cost;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+                    const float ocost = __shfl_xor_sync(0xffffffffu, bcost, o);
+                    const int oh = __shfl_xor_sync(0xffffffffu, bh, o);
+                    const bool better = oc > bc || (oc == bc && (ocost < bcost || (ocost == bcost && oh < bh)));
+                    if (better) { bc = oc; bcost = ocost; bh = oh; }
+                }
+                if (bh == hyp) {
+                    sh.warp_cnt[warp] = bc;
+                    sh.warp_cost[warp] = bcost;
+                    sh.warp_hyp[warp] = bh;
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) sh.warpF[warp][i] = ok ? F[i] : 0.f;
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    int bw = -1;
+                    int cc = sh.best_cnt;
+                    float cs = sh.best_cost;
+                    for (int w = 0; w < kWarps; ++w) {
+                        if (sh.warp_cnt[w] > cc || (sh.warp_cnt[w] == cc && sh.warp_cost[w] < cs)) {
+                            cc = sh.warp_cnt[w];
+                            cs = sh.warp_cost[w];
+                            bw = w;
+                        }
+                    }
+                    if (bw >= 0) {
+                        sh.best_cnt = cc;
+                        sh.best_cost = cs;
+                        for (int i = 0; i < 9; ++i) sh.bestF[i] = sh.warpF[bw][i];
+                    }
+                    const int need = rc::iters_needed(sh.best_cnt, m, prm.confidence, max_iters);
+                    sh.need = need;
+                }
+                done += kWarps * 32;
+                __syncthreads();
+            }
+            ransac_it = done < max_iters ? done : max_iters;
+            if (sh.best_cnt < kMinSample) {
+                write_skip(p, m, SFM_PAIR_NO_MODEL, F_out, metrics, status_out);
+                continue;
+            }
+            ransac_inl = sh.best_cnt;
+            if (threadIdx.x < 9) sh.Fd[threadIdx.x] = static_cast<double>(sh.bestF[threadIdx.x]);
+            __syncthreads();
+
+            // ------------------------------------------------ inlier refits
+            for (int it = 0; it < prm.lo_iters; ++it) {
+                float Ff[9];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) Ff[i] = static_cast<float>(sh.Fd[i]);
+                double mom[5] = {0, 0, 0, 0, 0};
+                for (int i = threadIdx.x; i < m; i += kThreads) {
+                    const float4 q = load_match(p1, p2, i);
+                    if (rc::sampson_sq<float>(Ff, q.x, q.y, q.z, q.w) < thr2) {
+                        mom[0] += 1.0; mom[1] += q.x; mom[2] += q.y; mom[3] += q.z; mom[4] += q.w;
+                    }
+                }
+                block_sum<5>(mom, sh);
+                const double n_in = mom[0];
+                if (n_in < 8.0) break;
+                const double c1x = mom[1] / n_in, c1y = mom[2] / n_in;
+                const double c2x = mom[3] / n_in, c2y = mom[4] / n_in;
+                double acc[47];
+#pragma unroll
+                for (int i = 0; i < 47; ++i) acc[i] = 0.0;
+                for (int i = threadIdx.x; i < m; i += kThreads) {
+                    const float4 q = load_match(p1, p2, i);
+                    if (rc::sampson_sq<float>(Ff, q.x, q.y, q.z, q.w) < thr2) {
+                        const double x1 = q.x - c1x, y1 = q.y - c1y, x2 = q.z - c2x, y2 = q.w - c2y;
+                        acc[45] += sqrt(x1 * x1 + y1 * y1);
+                        acc[46] += sqrt(x2 * x2 + y2 * y2);
+                        double a[9];
+                        rc::design_row(x1, y1, x2, y2, a);
+                        int k = 0;
+#pragma unroll
+                        for (int r = 0; r < 9; ++r)
+#pragma unroll
+                            for (int c = r; c < 9; ++c) acc[k++] += a[r] * a[c];
+                    }
+                }
+                block_sum<47>(acc, sh);
+                if (threadIdx.x == 0) {
+                    sh.flag = 0;
+                    if (acc[45] > 1e-9 && acc[46] > 1e-9) {
+                        const double s1 = 1.4142135623730951 * n_in / acc[45];
+                        const double s2 = 1.4142135623730951 * n_in / acc[46];
+                        const double wgt[9] = {s1 * s2, s1 * s2, s2, s1 * s2, s1 * s2, s2, s1, s1, 1.0};
+                        double ata[45];
+                        int k = 0;
+                        for (int r = 0; r < 9; ++r)
+                            for (int c = r; c < 9; ++c) {
+                                ata[k] = acc[k] * wgt[r] * wgt[c];
+                                ++k;
+                            }
+                        double Fn[9];
+                        if (rc::refit_from_normal(ata, c1x, c1y, s1, c2x, c2y, s2, Fn)) {
+                            for (int i = 0; i < 9; ++i) sh.res[i] = Fn[i];
+                            sh.flag = 1;
+                        }
+                    }
+                }
+                __syncthreads();
+                if (!sh.flag) break;
+                float Fn[9];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) Fn[i] = static_cast<float>(sh.res[i]);
+                __syncthreads();
+                double sc[2] = {0, 0};
+                for (int i = threadIdx.x; i < m; i += kThreads) {
+                    const float4 q = load_match(p1, p2, i);
+                    const float e = rc::sampson_sq<float>(Fn, q.x, q.y, q.z, q.w);
+                    sc[0] += e < thr2 ? 1.0 : 0.0;
+                    sc[1] += fminf(e, thr2);
+                }
+                block_sum<2>(sc, sh);
+                const int new_cnt = static_cast<int>(sc[0]);
+                const bool accept = new_cnt > sh.best_cnt ||
+                                    (new_cnt == sh.best_cnt && static_cast<float>(sc[1]) < sh.best_cost);
+                __syncthreads();
+                if (!accept) break;
+                if (threadIdx.x < 9) sh.Fd[threadIdx.x] = static_cast<double>(Fn[threadIdx.x]);
+                if (threadIdx.x == 0) {
+                    sh.best_cnt = new_cnt;
+                    sh.best_cost = static_cast<float>(sc[1]);
+                }
+                __syncthreads();
+            }
+            ransac_inl = sh.best_cnt;
+            if (threadIdx.x == 0) {
+                double Fn[9];
+                for (int i = 0; i < 9; ++i) Fn[i] = sh.Fd[i];
+                rc::enforce_rank2<double>(Fn);     // exact rank 2 in float64
+                rc::normalise_f22(Fn);
+                for (int i = 0; i < 9; ++i) sh.Fd[i] = Fn[i];
+            }
+            __syncthreads();
+            if (threadIdx.x < 9) F_out[9ll * p + threadIdx.x] = sh.Fd[threadIdx.x];
+        }
+
+        // ---------------------------------------------------- K4 verification
+        double Fv[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) Fv[i] = sh.Fd[i];
+        const float vthr = static_cast<float>(prm.verify_thresh);
+        double st[11];
+#pragma unroll
+        for (int i = 0; i < 11; ++i) st[i] = 0.0;
+        for (int i = threadIdx.x; i < m; i += kThreads) {
+            const float4 q = load_match(p1, p2, i);
+            const float e = symmetric_error(Fv, q.x, q.y, q.z, q.w);
+            const bool in = e < vthr;
+            sym[base + i] = e;
+            mask[base + i] = in ? 1 : 0;
+            st[1] += e;
+            if (in) {
+                st[0] += 1.0;
+                st[2] += e;
+                st[3] += q.x; st[4] += q.y; st[5] += q.z; st[6] += q.w;
+                st[7] += static_cast<double>(q.x) * q.x; st[8] += static_cast<double>(q.y) * q.y;
+                st[9] += static_cast<double>(q.z) * q.z; st[10] += static_cast<double>(q.w) * q.w;
+            }
+        }
+        block_sum<11>(st, sh);
+        if (threadIdx.x == 0) {
+            const double n_in = st[0];
+            sfm_pair_metrics mt;
+            mt.total_matches = m;
+            mt.inliers = static_cast<int>(n_in);
+            const double ratio = m > 0 ? n_in / m : 0.0;
+            mt.inlier_ratio = static_cast<float>(ratio);
+            mt.reprojection_error = n_in > 0 ? static_cast<float>(st[2] / n_in) : __int_as_float(0x7f800000);
+            mt.symmetric_error = m > 0 ? static_cast<float>(st[1] / m) : 0.f;
+            bool spread = n_in > 0;
+            if (spread) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const double mean = st[3 + k] / n_in;
+                    double var = st[7 + k] / n_in - mean * mean;
+                    var = var > 0 ? var : 0;
+                    spread = spread && (static_cast<float>(sqrt(var)) > static_cast<float>(prm.min_spread));
+                }
+            }
+            mt.well_distributed = spread ? 1 : 0;
+            mt.ransac_inliers = ransac_inl;
+            mt.ransac_iters = ransac_it;
+            metrics[p] = mt;
+            const bool pass = mt.inliers >= prm.min_inliers && ratio >= prm.min_ratio &&
+                              mt.reprojection_error <= static_cast<float>(prm.max_error) && spread;
+            status_out[p] = pass ? SFM_PAIR_OK : SFM_PAIR_QUALITY_FAIL;
+        }
+    }
+}
+
+__global__ void gather_points_kernel(const int32_t* __restrict__ pairs, int n_pairs,
+                                     const long long* __restrict__ img_off,
+                                     const long long* __restrict__ row_off,
+                                     const int32_t* __restrict__ mq, const int32_t* __restrict__ mt,
+                                     const int32_t* __restrict__ count, const float2* __restrict__ kps,
+                                     float2* __restrict__ pts1, float2* __restrict__ pts2) {
+    for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+        const long long q0 = img_off[pairs[2 * p]], t0 = img_off[pairs[2 * p + 1]];
+        const long long base = row_off[p];
+        const int m = count[p];
+        for (int i = threadIdx.x; i < m; i += blockDim.x) {
+            pts1[base + i] = __ldg(kps + q0 + mq[base + i]);
+            pts2[base + i] = __ldg(kps + t0 + mt[base + i]);
+        }
+    }
+}
+
+}  // namespace
+
+void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
+                          const int64_t* d_row_off, const int32_t* d_mq, const int32_t* d_mt,
+                          const int32_t* d_count, const float* d_kps, float* d_pts1, float* d_pts2,
+                          cudaStream_t st, int64_t* launches) {
+    if (n_pairs <= 0) return;
+    const int grid = n_pairs < 148 * 8 ? n_pairs : 148 * 8;
+    gather_points_kernel<<<grid, 256, 0, st>>>(
+        d_pairs, n_pairs, reinterpret_cast<const long long*>(d_img_off),
+        reinterpret_cast<const long long*>(d_row_off), d_mq, d_mt, d_count,
+        reinterpret_cast<const float2*>(d_kps), reinterpret_cast<float2*>(d_pts1),
+        reinterpret_cast<float2*>(d_pts2));
+    ++*launches;
+}
+
+int launch_ransac_verify(int32_t n_pairs, const int64_t* d_off, const int32_t* d_cnt,
+                             const int32_t* d_pair_ids, const float* d_pts1, const float* d_pts2,
+                             const double* d_F_in, const sfm_verify_params& prm, double* d_F,
+                             uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics,
+                             int32_t* d_status, cudaStream_t st, int64_t* launches) {
+    if (n_pairs <= 0) return 0;
+    const int grid = n_pairs < 148 * 4 ? n_pairs : 148 * 4;
+    ransac_verify_kernel<<<grid, kThreads, 0, st>>>(
+        n_pairs, reinterpret_cast<const long long*>(d_off), d_cnt, d_pair_ids, d_pts1, d_pts2, d_F_in,
+        prm, d_F, d_mask, d_sym, d_metrics, d_status);
+    ++*launches;
+    return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace sfm

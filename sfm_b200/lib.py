@@ -1,0 +1,294 @@
+"""ctypes binding of libsfm_match.so (C ABI in include/sfm_match.h).
+
+PyTorch is used only to own device memory and streams; every compute call goes
+through the C ABI into hand-written sm_100a kernels.  There is no CPU or eager
+fallback: if the library or a CUDA device is missing, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libsfm_match.so"
+ABI_VERSION = 1
+
+QBLOCK = 256
+TTILE = 128
+INT32_MAX = 2**31 - 1
+
+PAIR_OK, PAIR_TOO_FEW_FEATURES, PAIR_TOO_FEW_MATCHES, PAIR_NO_MODEL, PAIR_QUALITY_FAIL = range(5)
+STATUS_NAMES = ("OK", "TOO_FEW_FEATURES", "TOO_FEW_MATCHES", "NO_MODEL", "QUALITY_FAIL")
+
+
+class VerifyParams(C.Structure):
+    """sfm_verify_params; defaults = the constants hard-coded in the reference
+    (utils/find_matches.py:157, :185, :203, :274, :282)."""
+    _fields_ = [
+        ("ransac_thresh", C.c_double), ("confidence", C.c_double),
+        ("max_iters", C.c_int32), ("min_matches", C.c_int32), ("seed", C.c_uint64),
+        ("verify_thresh", C.c_double), ("min_inliers", C.c_int32), ("lo_iters", C.c_int32),
+        ("min_ratio", C.c_double), ("max_error", C.c_double), ("min_spread", C.c_double),
+    ]
+
+
+METRICS_DTYPE = np.dtype([
+    ("total_matches", np.int32), ("inliers", np.int32), ("inlier_ratio", np.float32),
+    ("reprojection_error", np.float32), ("symmetric_error", np.float32),
+    ("well_distributed", np.int32), ("ransac_inliers", np.int32), ("ransac_iters", np.int32),
+])
+
+# every symbol include/sfm_match.h declares
+EXPORTS = (
+    "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
+    "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
+    "sfm_ransac_points", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
+)
+
+_lib = None
+
+
+class SfmError(RuntimeError):
+    pass
+
+
+def load_library(path: Path | None = None) -> C.CDLL:
+    """dlopen the in-tree library and declare the prototypes.  Raises if absent."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise SfmError(f"{p} is missing: run `python -m sfm_b200.build` (nvcc, sm_100a). "
+                       "There is no CPU fallback for the matching path.")
+    lib = C.CDLL(str(p))
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    lib.sfm_abi_version.restype = C.c_int
+    lib.sfm_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.sfm_destroy.argtypes = [vp]
+    lib.sfm_destroy.restype = None
+    lib.sfm_last_error.argtypes = [vp]
+    lib.sfm_last_error.restype = C.c_char_p
+    lib.sfm_default_params.argtypes = [C.POINTER(VerifyParams)]
+    lib.sfm_default_params.restype = None
+    lib.sfm_set_images.argtypes = [vp, vp, vp, vp, i32, vp]
+    lib.sfm_knn2.argtypes = [vp, vp, i32, vp, vp, vp]
+    lib.sfm_filter_matches.argtypes = [vp, vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp, vp, vp]
+    lib.sfm_verify_pairs.argtypes = [vp, vp, i32, vp, vp, vp, vp, C.POINTER(VerifyParams),
+                                     vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.sfm_verify_given_F.argtypes = [vp, i32, vp, vp, vp, vp, C.POINTER(VerifyParams),
+                                       vp, vp, vp, vp, vp]
+    lib.sfm_ransac_points.argtypes = [vp, i32, vp, vp, vp, C.POINTER(VerifyParams),
+                                      vp, vp, vp, vp, vp, vp]
+    lib.sfm_launch_count.argtypes = [vp]
+    lib.sfm_launch_count.restype = i64
+    lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
+    lib.sfm_debug_dot_tile.argtypes = [vp, i64, i64, vp, vp]
+    for name in EXPORTS:
+        getattr(lib, name)
+    if lib.sfm_abi_version() != ABI_VERSION:
+        raise SfmError("libsfm_match.so ABI version mismatch; rebuild")
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def default_params(**overrides) -> VerifyParams:
+    p = VerifyParams()
+    load_library().sfm_default_params(C.byref(p))
+    for k, v in overrides.items():
+        if not hasattr(p, k):
+            raise AttributeError(k)
+        setattr(p, k, v)
+    return p
+
+
+def _h(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _i64(a) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(a, dtype=np.int64))
+
+
+def _pairs(a) -> np.ndarray:
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.int32)).reshape(-1, 2)
+    return a
+
+
+class Context:
+    """One sfm_ctx: one GPU, one host thread."""
+
+    def __init__(self, device: int = 0):
+        import torch
+        if not torch.cuda.is_available():
+            raise SfmError("no CUDA device: the matching path has no CPU fallback")
+        self.torch = torch
+        self.lib = load_library()
+        self.device = torch.device("cuda", device)
+        h = C.c_void_p()
+        if self.lib.sfm_create(device, C.byref(h)) != 0:
+            raise SfmError(self.lib.sfm_last_error(None).decode())
+        self.h = h
+        self._keep = None
+        self.offsets = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.sfm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- helpers
+    def _check(self, rc: int):
+        if rc != 0:
+            raise SfmError(self.lib.sfm_last_error(self.h).decode())
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _dev(self, t, dtype):
+        torch = self.torch
+        if t.device != self.device or t.dtype != dtype or not t.is_contiguous():
+            raise SfmError(f"expected contiguous {dtype} tensor on {self.device}")
+        return C.c_void_p(t.data_ptr())
+
+    def empty(self, shape, dtype):
+        return self.torch.empty(shape, dtype=dtype, device=self.device)
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.sfm_launch_count(self.h))
+
+    # -- image set
+    def set_images(self, desc, kps, offsets):
+        """desc u8 [R,128] cuda, kps f32 [R,2] cuda or None, offsets int64 [N+1] (host)."""
+        torch = self.torch
+        off = _i64(offsets.cpu().numpy() if hasattr(offsets, "cpu") else offsets)
+        if desc.dim() != 2 or desc.shape[1] != 128:
+            raise SfmError("desc must be [rows, 128] uint8")
+        if int(off[-1]) != desc.shape[0]:
+            raise SfmError("offsets[-1] must equal the number of descriptor rows")
+        if kps is not None and tuple(kps.shape) != (desc.shape[0], 2):
+            raise SfmError("kps must be [rows, 2] float32")
+        dptr = self._dev(desc, torch.uint8) if desc.numel() else C.c_void_p(0)
+        kptr = self._dev(kps, torch.float32) if kps is not None and kps.numel() else C.c_void_p(0)
+        self._check(self.lib.sfm_set_images(self.h, dptr, kptr, _h(off), len(off) - 1, self._stream()))
+        self._keep = (desc, kps)
+        self.offsets = off
+        self.counts = np.diff(off)
+
+    def query_rows(self, pairs) -> np.ndarray:
+        """int64 [P+1] output row offsets: pair p owns n_query(p) rows."""
+        pairs = _pairs(pairs)
+        ro = np.zeros(len(pairs) + 1, np.int64)
+        np.cumsum(self.counts[pairs[:, 0]], out=ro[1:])
+        return ro
+
+    # -- K1
+    def knn2(self, pairs, row_off=None, out=None):
+        """Directed pairs -> i32 [rows,4] (idx1, idx2, d1^2, d2^2) on the device."""
+        torch = self.torch
+        pairs = _pairs(pairs)
+        row_off = self.query_rows(pairs) if row_off is None else _i64(row_off)
+        if out is None:
+            out = self.empty((int(row_off[-1]), 4), torch.int32)
+        self._check(self.lib.sfm_knn2(self.h, _h(pairs), len(pairs), _h(row_off),
+                                      self._dev(out, torch.int32), self._stream()))
+        return out, row_off
+
+    # -- K2
+    def filter_matches(self, pairs, row_off, knn, ratio=0.75, row_off_rev=None, knn_rev=None, out=None):
+        torch = self.torch
+        pairs = _pairs(pairs)
+        row_off = _i64(row_off)
+        n = int(row_off[-1])
+        if out is None:
+            out = (self.empty((n,), torch.int32), self.empty((n,), torch.int32),
+                   self.empty((n,), torch.int32), self.empty((len(pairs),), torch.int32))
+        mq, mt, md2, cnt = out
+        rev_off = _i64(row_off_rev) if knn_rev is not None else None
+        self._check(self.lib.sfm_filter_matches(
+            self.h, _h(pairs), len(pairs), _h(row_off), self._dev(knn, torch.int32),
+            _h(rev_off) if rev_off is not None else C.c_void_p(0),
+            self._dev(knn_rev, torch.int32) if knn_rev is not None else C.c_void_p(0),
+            float(ratio), self._dev(mq, torch.int32), self._dev(mt, torch.int32),
+            self._dev(md2, torch.int32), self._dev(cnt, torch.int32), self._stream()))
+        return mq, mt, md2, cnt
+
+    # -- K3 + K4
+    def _verify_outputs(self, n_pairs, n_rows, need_F=True):
+        torch = self.torch
+        return dict(
+            F=self.empty((n_pairs, 9), torch.float64) if need_F else None,
+            mask=self.empty((n_rows,), torch.uint8),
+            sym=self.empty((n_rows,), torch.float32),
+            metrics=self.empty((n_pairs, METRICS_DTYPE.itemsize), torch.uint8),
+            status=self.empty((n_pairs,), torch.int32),
+        )
+
+    def verify_pairs(self, pairs, row_off, mq, mt, count, params=None):
+        torch = self.torch
+        pairs = _pairs(pairs)
+        row_off = _i64(row_off)
+        n = int(row_off[-1])
+        o = self._verify_outputs(len(pairs), n)
+        o["pts1"] = self.empty((n, 2), torch.float32)
+        o["pts2"] = self.empty((n, 2), torch.float32)
+        prm = params if params is not None else default_params()
+        self._check(self.lib.sfm_verify_pairs(
+            self.h, _h(pairs), len(pairs), _h(row_off), self._dev(mq, torch.int32),
+            self._dev(mt, torch.int32), self._dev(count, torch.int32), C.byref(prm),
+            self._dev(o["pts1"], torch.float32), self._dev(o["pts2"], torch.float32),
+            self._dev(o["F"], torch.float64), self._dev(o["mask"], torch.uint8),
+            self._dev(o["sym"], torch.float32), self._dev(o["metrics"], torch.uint8),
+            self._dev(o["status"], torch.int32), self._stream()))
+        return o
+
+    def verify_given_F(self, off, pts1, pts2, F, params=None):
+        torch = self.torch
+        off = _i64(off)
+        o = self._verify_outputs(len(off) - 1, int(off[-1]), need_F=False)
+        prm = params if params is not None else default_params()
+        self._check(self.lib.sfm_verify_given_F(
+            self.h, len(off) - 1, _h(off), self._dev(pts1, torch.float32),
+            self._dev(pts2, torch.float32), self._dev(F, torch.float64), C.byref(prm),
+            self._dev(o["mask"], torch.uint8), self._dev(o["sym"], torch.float32),
+            self._dev(o["metrics"], torch.uint8), self._dev(o["status"], torch.int32), self._stream()))
+        return o
+
+    def ransac_points(self, off, pts1, pts2, params=None):
+        torch = self.torch
+        off = _i64(off)
+        o = self._verify_outputs(len(off) - 1, int(off[-1]))
+        prm = params if params is not None else default_params()
+        self._check(self.lib.sfm_ransac_points(
+            self.h, len(off) - 1, _h(off), self._dev(pts1, torch.float32),
+            self._dev(pts2, torch.float32), C.byref(prm), self._dev(o["F"], torch.float64),
+            self._dev(o["mask"], torch.uint8), self._dev(o["sym"], torch.float32),
+            self._dev(o["metrics"], torch.uint8), self._dev(o["status"], torch.int32), self._stream()))
+        return o
+
+    # -- measurement / debug
+    def probe_int8_peak(self, iters=4096):
+        ms, ops = C.c_float(), C.c_double()
+        self._check(self.lib.sfm_probe_int8_peak(self.h, iters, C.byref(ms), C.byref(ops), self._stream()))
+        return ops.value / (ms.value * 1e-3) / 1e12, ms.value   # TOP/s, ms
+
+    def debug_dot_tile(self, q_row, t_row):
+        out = self.empty((128, 128), self.torch.int32)
+        self._check(self.lib.sfm_debug_dot_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
+                                                self._stream()))
+        return out
+
+
+def metrics_to_numpy(t) -> np.ndarray:
+    """uint8 [P, 32] device tensor -> structured array (METRICS_DTYPE)."""
+    return t.cpu().numpy().view(METRICS_DTYPE).reshape(-1)
