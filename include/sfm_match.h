@@ -63,6 +63,11 @@ typedef struct sfm_verify_params {
     double min_ratio;       /* 0.3 */
     double max_error;       /* 2.0 */
     double min_spread;      /* 20    utils/find_matches.py:185 */
+    int32_t score_mode;     /* bit 0: hypotheses scored by the symmetric epipolar error instead of
+                               Sampson; bit 1: the inlier refits use the symmetric error (the
+                               measure geometric_verification applies, :165-172) */
+    int32_t min_work;       /* 262144: floor on hypotheses x matches before the adaptive stop may
+                               end the search (at most 4096 hypotheses); 0 disables */
 } sfm_verify_params;
 
 /* Per-pair metrics, the dict returned by ImageMatcher.geometric_verification
@@ -160,6 +165,23 @@ SFM_API int sfm_ransac_points(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_of
                       const sfm_verify_params* params, double* d_F, uint8_t* d_mask,
                       float* d_sym, sfm_pair_metrics* d_metrics, int32_t* d_status,
                       void* stream);
+
+/* ---- result packing ---------------------------------------------------- */
+/* The arenas above are sized for the worst case (one match per query row).
+ * Before the device->host copy, gather the `d_count[p]` valid entries of every
+ * kept pair (all pairs, or only those with d_status == SFM_PAIR_OK when
+ * only_ok != 0) into dense arrays -- what save_pair_data
+ * (utils/find_matches.py:312-327) writes for passing pairs.
+ *   d_pack_off i64 [n_pairs + 1] (out) dense offsets; [n_pairs] = total kept
+ * Any source pointer may be NULL (that array is skipped); each destination
+ * must hold as many elements as its source arena. */
+SFM_API int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row_off,
+                     const int32_t* d_count, const int32_t* d_status, int32_t only_ok,
+                     const int32_t* d_mq, const int32_t* d_mt, const int32_t* d_md2,
+                     const uint8_t* d_mask, const float* d_sym, const float* d_pts1,
+                     const float* d_pts2, int64_t* d_pack_off, int32_t* o_mq, int32_t* o_mt,
+                     int32_t* o_md2, uint8_t* o_mask, float* o_sym, float* o_pts1, float* o_pts2,
+                     void* stream);
 
 /* ---- measurement helpers ---------------------------------------------- */
 /* Number of kernel launches issued by this context since creation. */

@@ -140,6 +140,8 @@ void sfm_default_params(sfm_verify_params* p) {
     p->min_ratio = 0.3;
     p->max_error = 2.0;
     p->min_spread = 20.0;
+    p->score_mode = 3;
+    p->min_work = 1 << 18;
 }
 
 const char* sfm_last_error(sfm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -384,6 +386,34 @@ int sfm_ransac_points(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off, const
     if (!d_F && n_pairs > 0) return ctx->fail("d_F is NULL");
     return points_entry(ctx, n_pairs, h_off, d_pts1, d_pts2, nullptr, params, d_F, d_mask, d_sym,
                         d_metrics, d_status, static_cast<cudaStream_t>(stream));
+}
+
+int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row_off, const int32_t* d_count,
+                     const int32_t* d_status, int32_t only_ok, const int32_t* d_mq,
+                     const int32_t* d_mt, const int32_t* d_md2, const uint8_t* d_mask,
+                     const float* d_sym, const float* d_pts1, const float* d_pts2,
+                     int64_t* d_pack_off, int32_t* o_mq, int32_t* o_mt, int32_t* o_md2,
+                     uint8_t* o_mask, float* o_sym, float* o_pts1, float* o_pts2, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_pairs < 0) return ctx->fail("n_pairs < 0");
+    if (n_pairs == 0) return 0;
+    if (!h_row_off || !d_count || !d_pack_off) return ctx->fail("NULL argument");
+    if (only_ok && !d_status) return ctx->fail("only_ok needs d_status");
+    if ((d_mq && !o_mq) || (d_mt && !o_mt) || (d_md2 && !o_md2) || (d_mask && !o_mask) ||
+        (d_sym && !o_sym) || (d_pts1 && !o_pts1) || (d_pts2 && !o_pts2))
+        return ctx->fail("a source array has no destination");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n1 = static_cast<size_t>(n_pairs) + 1;
+    SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p + n1, h_row_off, sizeof(int64_t) * n1,
+                                  cudaMemcpyHostToDevice, st));
+    sfm::PackArrays a{d_mq, d_mt, d_md2, d_mask, d_sym, d_pts1, d_pts2,
+                      o_mq, o_mt, o_md2, o_mask, o_sym, o_pts1, o_pts2};
+    sfm::launch_pack(n_pairs, ctx->d_meta.p + n1, d_count, d_status, only_ok ? 1 : 0, d_pack_off, a, st,
+                     &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    return 0;
 }
 
 int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream) {

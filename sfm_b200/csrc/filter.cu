@@ -77,6 +77,53 @@ filter_kernel(const int32_t* __restrict__ pairs, int n_pairs, const long long* _
     }
 }
 
+
+// ---------------------------------------------------------------------------
+// Result packing: the per-pair arenas are sized for the worst case (one match
+// per query row); before the device->host copy the kept entries of the kept
+// pairs are gathered into dense arrays.  Exclusive scan of the kept counts by
+// one CTA, then one CTA per pair copies its slice with coalesced accesses.
+__global__ void __launch_bounds__(1024)
+pack_scan_kernel(const int32_t* __restrict__ count, const int32_t* __restrict__ status, int only_ok,
+                 int n_pairs, long long* __restrict__ pack_off) {
+    __shared__ long long part[1024];
+    const int per = (n_pairs + 1023) / 1024;
+    const int lo = threadIdx.x * per, hi = min(n_pairs, lo + per);
+    long long s = 0;
+    for (int p = lo; p < hi; ++p) s += (!only_ok || status[p] == SFM_PAIR_OK) ? count[p] : 0;
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const long long v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    long long run = part[threadIdx.x] - s;
+    for (int p = lo; p < hi; ++p) {
+        pack_off[p] = run;
+        run += (!only_ok || status[p] == SFM_PAIR_OK) ? count[p] : 0;
+    }
+    if (threadIdx.x == 1023) pack_off[n_pairs] = part[1023];
+}
+
+__global__ void pack_gather_kernel(int n_pairs, const long long* __restrict__ row_off,
+                                   const long long* __restrict__ pack_off, PackArrays a) {
+    for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+        const long long src = row_off[p], dst = pack_off[p];
+        const int n = static_cast<int>(pack_off[p + 1] - dst);
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            if (a.mq) a.o_mq[dst + i] = a.mq[src + i];
+            if (a.mt) a.o_mt[dst + i] = a.mt[src + i];
+            if (a.md2) a.o_md2[dst + i] = a.md2[src + i];
+            if (a.mask) a.o_mask[dst + i] = a.mask[src + i];
+            if (a.sym) a.o_sym[dst + i] = a.sym[src + i];
+            if (a.pts1) reinterpret_cast<float2*>(a.o_pts1)[dst + i] = reinterpret_cast<const float2*>(a.pts1)[src + i];
+            if (a.pts2) reinterpret_cast<float2*>(a.o_pts2)[dst + i] = reinterpret_cast<const float2*>(a.pts2)[src + i];
+        }
+    }
+}
+
 }  // namespace
 
 void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
@@ -90,6 +137,19 @@ void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img
         reinterpret_cast<const long long*>(d_row_off), d_knn,
         reinterpret_cast<const long long*>(d_row_off_rev), d_knn_rev, ratio, d_mq, d_mt, d_md2,
         d_count);
+    ++*launches;
+}
+
+void launch_pack(int32_t n_pairs, const int64_t* d_row_off, const int32_t* d_count,
+                 const int32_t* d_status, int only_ok, int64_t* d_pack_off, const PackArrays& a,
+                 cudaStream_t st, int64_t* launches) {
+    if (n_pairs <= 0) return;
+    pack_scan_kernel<<<1, 1024, 0, st>>>(d_count, d_status, only_ok, n_pairs,
+                                         reinterpret_cast<long long*>(d_pack_off));
+    ++*launches;
+    const int grid = n_pairs < 148 * 8 ? n_pairs : 148 * 8;
+    pack_gather_kernel<<<grid, 256, 0, st>>>(n_pairs, reinterpret_cast<const long long*>(d_row_off),
+                                             reinterpret_cast<const long long*>(d_pack_off), a);
     ++*launches;
 }
 

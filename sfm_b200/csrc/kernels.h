@@ -41,6 +41,19 @@ void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img
                    const int4* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,
                    int32_t* d_md2, int32_t* d_count, cudaStream_t st, int64_t* launches);
 
+struct PackArrays {
+    const int32_t *mq, *mt, *md2;
+    const uint8_t* mask;
+    const float *sym, *pts1, *pts2;
+    int32_t *o_mq, *o_mt, *o_md2;
+    uint8_t* o_mask;
+    float *o_sym, *o_pts1, *o_pts2;
+};
+// d_status may be NULL when only_ok == 0.
+void launch_pack(int32_t n_pairs, const int64_t* d_row_off, const int32_t* d_count,
+                 const int32_t* d_status, int only_ok, int64_t* d_pack_off, const PackArrays& a,
+                 cudaStream_t st, int64_t* launches);
+
 // ---- ransac.cu
 void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
                           const int64_t* d_row_off, const int32_t* d_mq, const int32_t* d_mt,

@@ -135,6 +135,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float thr2 = static_cast<float>(prm.ransac_thresh * prm.ransac_thresh);
     const int max_iters = (prm.max_iters + 31) & ~31;
+    const bool hyp_sym = (prm.score_mode & 1) != 0, lo_sym = (prm.score_mode & 2) != 0;
 
     for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
         __syncthreads();
@@ -158,10 +159,14 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
             }
             const uint64_t key = pair_ids ? rc::pair_key(prm.seed, pair_ids[2 * p], pair_ids[2 * p + 1])
                                           : rc::pair_key(prm.seed, static_cast<uint32_t>(p), 0xffffffffu);
+            // small pairs are cheap: never stop before hypotheses x matches >= min_work
+            int floor_h = prm.min_work > 0 ? ((prm.min_work + m - 1) / m + 255) & ~255 : 0;
+            floor_h = floor_h > 4096 ? 4096 : floor_h;
+            const int limit = max_iters > floor_h ? max_iters : floor_h;
             if (threadIdx.x == 0) {
                 sh.best_cnt = -1;
                 sh.best_cost = FLT_MAX;
-                sh.need = max_iters;
+                sh.need = limit;
             }
             const bool resident = m <= kChunk;
             if (resident)
@@ -174,7 +179,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                 const int hyp = done + warp * 32 + lane;
                 float F[9];
                 bool ok = false;
-                if (hyp < max_iters) {
+                if (hyp < limit) {
                     uint32_t idx[8];
                     rc::sample8(key, hyp, m, idx);
                     float s[8][4];
@@ -199,7 +204,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
 #pragma unroll 4
                         for (int i = 0; i < n; ++i) {
                             const float4 q = sh.pts[i];
-                            const float e = rc::sampson_sq<float>(F, q.x, q.y, q.z, q.w);
+                            const float e = rc::residual_sq<float>(F, q.x, q.y, q.z, q.w, hyp_sym);
                             c += e < thr2;
                             cost += fminf(e, thr2);
                         }
@@ -242,12 +247,12 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                         for (int i = 0; i < 9; ++i) sh.bestF[i] = sh.warpF[bw][i];
                     }
                     const int need = rc::iters_needed(sh.best_cnt, m, prm.confidence, max_iters);
-                    sh.need = need;
+                    sh.need = need > floor_h ? need : floor_h;
                 }
                 done += kWarps * 32;
                 __syncthreads();
             }
-            ransac_it = done < max_iters ? done : max_iters;
+            ransac_it = done < limit ? done : limit;
             if (sh.best_cnt < kMinSample) {
                 write_skip(p, m, SFM_PAIR_NO_MODEL, F_out, metrics, status_out);
                 continue;
@@ -264,7 +269,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                 double mom[5] = {0, 0, 0, 0, 0};
                 for (int i = threadIdx.x; i < m; i += kThreads) {
                     const float4 q = load_match(p1, p2, i);
-                    if (rc::sampson_sq<float>(Ff, q.x, q.y, q.z, q.w) < thr2) {
+                    if (rc::residual_sq<float>(Ff, q.x, q.y, q.z, q.w, lo_sym) < thr2) {
                         mom[0] += 1.0; mom[1] += q.x; mom[2] += q.y; mom[3] += q.z; mom[4] += q.w;
                     }
                 }
@@ -278,7 +283,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                 for (int i = 0; i < 47; ++i) acc[i] = 0.0;
                 for (int i = threadIdx.x; i < m; i += kThreads) {
                     const float4 q = load_match(p1, p2, i);
-                    if (rc::sampson_sq<float>(Ff, q.x, q.y, q.z, q.w) < thr2) {
+                    if (rc::residual_sq<float>(Ff, q.x, q.y, q.z, q.w, lo_sym) < thr2) {
                         const double x1 = q.x - c1x, y1 = q.y - c1y, x2 = q.z - c2x, y2 = q.w - c2y;
                         acc[45] += sqrt(x1 * x1 + y1 * y1);
                         acc[46] += sqrt(x2 * x2 + y2 * y2);
@@ -321,7 +326,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                 double sc[2] = {0, 0};
                 for (int i = threadIdx.x; i < m; i += kThreads) {
                     const float4 q = load_match(p1, p2, i);
-                    const float e = rc::sampson_sq<float>(Fn, q.x, q.y, q.z, q.w);
+                    const float e = rc::residual_sq<float>(Fn, q.x, q.y, q.z, q.w, lo_sym);
                     sc[0] += e < thr2 ? 1.0 : 0.0;
                     sc[1] += fminf(e, thr2);
                 }

@@ -235,6 +235,32 @@ SFM_HD T sampson_sq(const T (&F)[9], T x1, T y1, T x2, T y2) {
     return den > T(0) ? (r * r) / den : T(1e30);
 }
 
+// Symmetric epipolar distance (mean of the two point-to-epiline distances),
+// the quantity thresholded by the reference's geometric_verification
+// (utils/find_matches.py:165-172); fast single-precision form for scoring.
+template <typename T>
+SFM_HD T symmetric_dist(const T (&F)[9], T x1, T y1, T x2, T y2) {
+    const T l2x = F[0] * x1 + F[1] * y1 + F[2];
+    const T l2y = F[3] * x1 + F[4] * y1 + F[5];
+    const T l2z = F[6] * x1 + F[7] * y1 + F[8];
+    const T l1x = F[0] * x2 + F[3] * y2 + F[6];
+    const T l1y = F[1] * x2 + F[4] * y2 + F[7];
+    const T r = fabs(x2 * l2x + y2 * l2y + l2z);
+    const T n1 = l1x * l1x + l1y * l1y, n2 = l2x * l2x + l2y * l2y;
+    if (!(n1 > T(0)) || !(n2 > T(0))) return T(1e15);
+    return T(0.5) * r * (T(1) / sqrt(n1) + T(1) / sqrt(n2));
+}
+
+// Residual used for inlier decisions: squared, compared against thr^2.
+template <typename T>
+SFM_HD T residual_sq(const T (&F)[9], T x1, T y1, T x2, T y2, bool symmetric) {
+    if (symmetric) {
+        const T d = symmetric_dist<T>(F, x1, y1, x2, y2);
+        return d * d;
+    }
+    return sampson_sq<T>(F, x1, y1, x2, y2);
+}
+
 // Standard adaptive stopping rule: hypotheses needed to draw one all-inlier
 // 8-sample with probability `conf` at inlier ratio w.
 SFM_HD int iters_needed(int inliers, int m, double conf, int max_iters) {

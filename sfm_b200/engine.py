@@ -1,0 +1,175 @@
+"""Batched pair engine: descriptors in, verified matches out.
+
+Sequences the kernels behind the C ABI for a list of image pairs -- the body of
+``ImageMatcher.process_image_pair`` from descriptors on (reference
+utils/find_matches.py:272-290) for a whole batch at once:
+
+    K1 sfm_knn2            (:144-147)  kNN k=2, forward (and reversed for mutual-NN)
+    K2 sfm_filter_matches  (:150-153)  ratio test (+ mutual) -> compact match lists
+    K3/K4 sfm_verify_pairs (:278-290)  gather, RANSAC F, verification, quality gate
+    sfm_pack_results                    dense arrays for the device->host copy
+
+PyTorch only owns memory and streams here.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import lib as L
+
+RATIO = 0.75           # utils/find_matches.py:152
+
+
+@dataclass
+class PairBatchResult:
+    """Host-side result of one batch (numpy).  Per-pair arrays are length P;
+    the dense arrays hold only the kept pairs' matches (see ``pack_off``)."""
+    pairs: np.ndarray            # int32 [P,2] image ids
+    status: np.ndarray           # int32 [P] lib.PAIR_*
+    count: np.ndarray            # int32 [P] matches after ratio(+mutual)
+    metrics: np.ndarray          # structured [P] (lib.METRICS_DTYPE)
+    F: np.ndarray                # float64 [P,3,3]
+    pack_off: np.ndarray         # int64 [P+1] offsets into the dense arrays
+    query_idx: np.ndarray        # int32 dense
+    train_idx: np.ndarray        # int32 dense
+    sq_dist: np.ndarray          # int32 dense
+    inlier_mask: np.ndarray      # bool dense
+    sym_err: np.ndarray          # float32 dense
+    pts1: np.ndarray             # float32 dense [.,2]
+    pts2: np.ndarray             # float32 dense [.,2]
+    timings_ms: dict = field(default_factory=dict)
+
+    def pair_slice(self, p: int) -> slice:
+        return slice(int(self.pack_off[p]), int(self.pack_off[p + 1]))
+
+    def distance(self, p: int) -> np.ndarray:
+        """``DMatch.distance`` values: float32 sqrt of the exact integer d^2."""
+        return np.sqrt(self.sq_dist[self.pair_slice(p)].astype(np.float32)).astype(np.float32)
+
+
+class PairEngine:
+    """One GPU's matcher: register an image set, then match pair batches."""
+
+    def __init__(self, device: int = 0, ratio: float = RATIO, mutual: bool = False,
+                 params: L.VerifyParams | None = None, max_rows_per_chunk: int = 48 << 20):
+        import torch
+        self.torch = torch
+        self.ctx = L.Context(device)
+        self.device = self.ctx.device
+        self.ratio = float(ratio)
+        self.mutual = bool(mutual)
+        self.params = params if params is not None else L.default_params()
+        self.max_rows = int(max_rows_per_chunk)
+        self.counts = None
+        self._bufs = {}
+
+    # ------------------------------------------------------------ image set
+    def set_images(self, desc, kps, offsets):
+        """desc u8 [R,128], kps f32 [R,2] (device tensors), offsets int64 [N+1] host."""
+        self.ctx.set_images(desc, kps, offsets)
+        self.counts = self.ctx.counts
+        self.n_images = len(self.counts)
+
+    def upload_images(self, desc_host, kps_host, offsets):
+        """Host (ideally pinned) tensors -> device, then register.  Returns bytes copied."""
+        torch = self.torch
+        d = desc_host.to(self.device, non_blocking=True)
+        k = kps_host.to(self.device, non_blocking=True)
+        self.set_images(d, k, offsets)
+        return desc_host.numel() * desc_host.element_size() + kps_host.numel() * kps_host.element_size()
+
+    def _buf(self, name, shape, dtype):
+        torch = self.torch
+        n = int(np.prod(shape))
+        cur = self._bufs.get(name)
+        if cur is None or cur.numel() < n or cur.dtype != dtype:
+            cur = torch.empty(max(n, 1), dtype=dtype, device=self.device)
+            self._bufs[name] = cur
+        return cur[:n].view(*shape)
+
+    # --------------------------------------------------------------- chunks
+    def _chunks(self, pairs):
+        rows = self.counts[pairs[:, 0]].astype(np.int64)
+        if self.mutual:
+            rows = np.maximum(rows, self.counts[pairs[:, 1]].astype(np.int64))
+        lo, acc = 0, 0
+        for p in range(len(pairs)):
+            if p > lo and acc + rows[p] > self.max_rows:
+                yield lo, p
+                lo, acc = p, 0
+            acc += rows[p]
+        if lo < len(pairs):
+            yield lo, len(pairs)
+
+    # ----------------------------------------------------------- device path
+    def match_device(self, pairs, only_ok: bool = True):
+        """Run K1..K4 + packing for one chunk; everything stays on the device.
+        Returns a dict of device tensors (views into reusable buffers)."""
+        torch, ctx = self.torch, self.ctx
+        pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
+        P = len(pairs)
+        ro = ctx.query_rows(pairs)
+        n = int(ro[-1])
+        knn = self._buf("knn", (n, 4), torch.int32)
+        ctx.knn2(pairs, ro, knn)
+        knn_rev = ro_rev = None
+        if self.mutual:
+            rev = np.ascontiguousarray(pairs[:, ::-1])
+            ro_rev = ctx.query_rows(rev)
+            knn_rev = self._buf("knn_rev", (int(ro_rev[-1]), 4), torch.int32)
+            ctx.knn2(rev, ro_rev, knn_rev)
+        out = (self._buf("mq", (n,), torch.int32), self._buf("mt", (n,), torch.int32),
+               self._buf("md2", (n,), torch.int32), self._buf("count", (P,), torch.int32))
+        mq, mt, md2, cnt = ctx.filter_matches(pairs, ro, knn, self.ratio, ro_rev, knn_rev, out=out)
+        v = ctx.verify_pairs(pairs, ro, mq, mt, cnt, self.params)
+        pack_off, dense = ctx.pack_results(ro, cnt, v["status"], only_ok, mq=mq, mt=mt, md2=md2,
+                                           mask=v["mask"], sym=v["sym"], pts1=v["pts1"], pts2=v["pts2"])
+        return dict(pairs=pairs, row_off=ro, knn=knn, count=cnt, status=v["status"], metrics=v["metrics"],
+                    F=v["F"], pack_off=pack_off, dense=dense)
+
+    # ------------------------------------------------------------- host path
+    def match_pairs(self, pairs, only_ok: bool = True) -> PairBatchResult:
+        """Public call: pair list in, host-side verified matches out (chunked)."""
+        torch = self.torch
+        pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
+        parts = []
+        for lo, hi in self._chunks(pairs):
+            d = self.match_device(pairs[lo:hi], only_ok)
+            total = int(d["pack_off"][-1].item())          # one sync per chunk
+            nt_small = self.counts[pairs[lo:hi, 1]] < 2
+            nq_zero = self.counts[pairs[lo:hi, 0]] < 1
+            status = d["status"].cpu().numpy()
+            # reference gate :268 and the Nt<2 failure of the ratio loop (:151)
+            status = np.where(nt_small | nq_zero, L.PAIR_TOO_FEW_FEATURES, status).astype(np.int32)
+            dn = d["dense"]
+            parts.append(dict(
+                pairs=pairs[lo:hi], status=status, count=d["count"].cpu().numpy(),
+                metrics=L.metrics_to_numpy(d["metrics"]), F=d["F"].cpu().numpy().reshape(-1, 3, 3),
+                pack_off=d["pack_off"].cpu().numpy(),
+                query_idx=dn["mq"][:total].cpu().numpy(), train_idx=dn["mt"][:total].cpu().numpy(),
+                sq_dist=dn["md2"][:total].cpu().numpy(), inlier_mask=dn["mask"][:total].cpu().numpy().astype(bool),
+                sym_err=dn["sym"][:total].cpu().numpy(), pts1=dn["pts1"][:total].cpu().numpy(),
+                pts2=dn["pts2"][:total].cpu().numpy()))
+        return _concat(parts, pairs)
+
+
+def _concat(parts, pairs) -> PairBatchResult:
+    if not parts:
+        z = np.zeros(0, np.int32)
+        return PairBatchResult(pairs=pairs, status=z, count=z, metrics=np.zeros(0, L.METRICS_DTYPE),
+                               F=np.zeros((0, 3, 3)), pack_off=np.zeros(1, np.int64), query_idx=z,
+                               train_idx=z, sq_dist=z, inlier_mask=np.zeros(0, bool),
+                               sym_err=np.zeros(0, np.float32), pts1=np.zeros((0, 2), np.float32),
+                               pts2=np.zeros((0, 2), np.float32))
+    offs, base = [np.zeros(1, np.int64)], 0
+    for q in parts:
+        offs.append(q["pack_off"][1:] + base)
+        base += int(q["pack_off"][-1])
+    cat = lambda k: np.concatenate([q[k] for q in parts])   # noqa: E731
+    return PairBatchResult(
+        pairs=pairs, status=cat("status"), count=cat("count"), metrics=cat("metrics"), F=cat("F"),
+        pack_off=np.concatenate(offs), query_idx=cat("query_idx"), train_idx=cat("train_idx"),
+        sq_dist=cat("sq_dist"), inlier_mask=cat("inlier_mask"), sym_err=cat("sym_err"),
+        pts1=cat("pts1"), pts2=cat("pts2"))

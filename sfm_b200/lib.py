@@ -31,6 +31,7 @@ class VerifyParams(C.Structure):
         ("max_iters", C.c_int32), ("min_matches", C.c_int32), ("seed", C.c_uint64),
         ("verify_thresh", C.c_double), ("min_inliers", C.c_int32), ("lo_iters", C.c_int32),
         ("min_ratio", C.c_double), ("max_error", C.c_double), ("min_spread", C.c_double),
+        ("score_mode", C.c_int32), ("min_work", C.c_int32),
     ]
 
 
@@ -44,7 +45,7 @@ METRICS_DTYPE = np.dtype([
 EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
-    "sfm_ransac_points", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
+    "sfm_ransac_points", "sfm_pack_results", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
 )
 
 _lib = None
@@ -82,6 +83,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
                                        vp, vp, vp, vp, vp]
     lib.sfm_ransac_points.argtypes = [vp, i32, vp, vp, vp, C.POINTER(VerifyParams),
                                       vp, vp, vp, vp, vp, vp]
+    lib.sfm_pack_results.argtypes = [vp, i32, vp, vp, vp, i32] + [vp] * 15 + [vp]
     lib.sfm_launch_count.argtypes = [vp]
     lib.sfm_launch_count.restype = i64
     lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
@@ -275,6 +277,34 @@ class Context:
             self._dev(o["mask"], torch.uint8), self._dev(o["sym"], torch.float32),
             self._dev(o["metrics"], torch.uint8), self._dev(o["status"], torch.int32), self._stream()))
         return o
+
+    def pack_results(self, row_off, count, status, only_ok, **arrays):
+        """Gather the valid entries of the kept pairs into dense device arrays.
+
+        arrays: any of mq, mt, md2 (int32), mask (uint8), sym, pts1, pts2 (float32).
+        Returns (pack_off int64 [P+1] device tensor, dict of dense tensors)."""
+        torch = self.torch
+        row_off = _i64(row_off)
+        n_pairs = len(row_off) - 1
+        dt = dict(mq=torch.int32, mt=torch.int32, md2=torch.int32, mask=torch.uint8,
+                  sym=torch.float32, pts1=torch.float32, pts2=torch.float32)
+        pack_off = self.empty((n_pairs + 1,), torch.int64)
+        src, dst, outs = [], [], {}
+        for name in ("mq", "mt", "md2", "mask", "sym", "pts1", "pts2"):
+            t = arrays.get(name)
+            if t is None:
+                src.append(C.c_void_p(0))
+                dst.append(C.c_void_p(0))
+            else:
+                o = torch.empty_like(t)
+                outs[name] = o
+                src.append(self._dev(t, dt[name]))
+                dst.append(self._dev(o, dt[name]))
+        self._check(self.lib.sfm_pack_results(
+            self.h, n_pairs, _h(row_off), self._dev(count, torch.int32),
+            self._dev(status, torch.int32) if status is not None else C.c_void_p(0),
+            1 if only_ok else 0, *src, C.c_void_p(pack_off.data_ptr()), *dst, self._stream()))
+        return pack_off, outs
 
     # -- measurement / debug
     def probe_int8_peak(self, iters=4096):

@@ -1,0 +1,163 @@
+"""GPU parity of K1 (kNN k=2) and K2 (ratio / mutual filter) through the C ABI,
+against the oracle and the golden vectors generated from cv2 (the reference's
+own call, utils/find_matches.py:144-153 with NORM_L2)."""
+import numpy as np
+import pytest
+
+from oracle import knn as oknn
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+INT32_MAX = 2**31 - 1
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from sfm_b200 import lib as L
+    c = L.Context(0)
+    yield c
+    c.close()
+
+
+def register(ctx, descs, kps=None):
+    counts = [len(d) for d in descs]
+    off = np.zeros(len(descs) + 1, np.int64)
+    off[1:] = np.cumsum(counts)
+    cat = np.concatenate([np.asarray(d, np.uint8).reshape(-1, 128) for d in descs]) if off[-1] else np.zeros((0, 128), np.uint8)
+    d = torch.from_numpy(cat).cuda()
+    k = None
+    if kps is not None:
+        k = torch.from_numpy(np.concatenate(kps).astype(np.float32)).cuda()
+    ctx.set_images(d, k, off)
+    return off
+
+
+def gpu_knn(ctx, pairs):
+    knn, ro = ctx.knn2(np.asarray(pairs, np.int32))
+    torch.cuda.synchronize()
+    return knn.cpu().numpy(), ro
+
+
+def check_pair(got, d1, d2):
+    idx, sqd = oknn.knn2_l2_numpy(d1, d2)
+    assert np.array_equal(got[:, :2], idx), "neighbour indices differ"
+    assert np.array_equal(got[:, 2:], sqd), "squared distances differ"
+
+
+@pytest.mark.parametrize("tag", ["rand", "ties", "dups", "tiny", "ragged"])
+def test_knn_golden_cv2_vectors(ctx, golden_dir, tag):
+    z = np.load(golden_dir / "knn_vectors.npz")
+    d1, d2 = z[tag + "_d1"], z[tag + "_d2"]
+    register(ctx, [d1, d2])
+    got, ro = gpu_knn(ctx, [(0, 1)])
+    assert np.array_equal(got[:, :2], z[tag + "_idx"])                       # bit-exact indices, cv2 tie rule
+    dist = np.sqrt(got[:, 2:].astype(np.float32))
+    assert np.array_equal(dist.view(np.uint32), z[tag + "_dist"].view(np.uint32))  # DMatch.distance bitwise
+    mq, mt, md2, cnt = ctx.filter_matches([(0, 1)], ro, torch.from_numpy(got).cuda())
+    n = int(cnt.cpu()[0])
+    assert np.array_equal(mq.cpu().numpy()[:n], z[tag + "_good_q"])
+    assert np.array_equal(mt.cpu().numpy()[:n], z[tag + "_good_t"])
+
+
+def test_knn_ragged_sizes_vs_oracle(ctx):
+    rng = np.random.default_rng(5)
+    sizes = [1, 2, 7, 14, 15, 52, 127, 128, 129, 255, 256, 257, 300, 500, 513, 1000]
+    descs = [rng.integers(0, 256, (n, 128)).astype(np.uint8) for n in sizes]
+    off = register(ctx, descs)
+    pairs = [(i, j) for i in range(len(sizes)) for j in range(len(sizes)) if i != j and sizes[j] >= 2]
+    got, ro = gpu_knn(ctx, pairs)
+    for p, (i, j) in enumerate(pairs):
+        check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+
+
+def test_knn_tiny_train_images(ctx):
+    rng = np.random.default_rng(6)
+    descs = [rng.integers(0, 256, (n, 128)).astype(np.uint8) for n in (40, 1, 0, 3)]
+    register(ctx, descs)
+    got, ro = gpu_knn(ctx, [(0, 1), (0, 2), (3, 1), (1, 0), (2, 0)])
+    a = got[ro[0]:ro[1]]                       # Nt = 1: best only
+    assert np.all(a[:, 0] == 0) and np.all(a[:, 1] == -1) and np.all(a[:, 3] == INT32_MAX)
+    want = ((descs[0].astype(np.int64) - descs[1][0].astype(np.int64)) ** 2).sum(1)
+    assert np.array_equal(a[:, 2], want)
+    b = got[ro[1]:ro[2]]                       # Nt = 0
+    assert np.all(b[:, :2] == -1) and np.all(b[:, 2:] == INT32_MAX)
+    assert ro[5] - ro[4] == 0                  # Nq = 0 -> no rows
+    check_pair(got[ro[3]:ro[4]], descs[1], descs[0])
+
+
+def test_knn_sift_like_ties_and_duplicates(ctx):
+    from sfm_b200 import synth
+    s = synth.make_image_set(4, [700, 900, 333, 1024], seed=77, tie_frac=0.05)
+    descs = [s.image(i)[0].numpy() for i in range(4)]
+    register(ctx, descs)
+    pairs = [(i, j) for i in range(4) for j in range(4)]     # includes self pairs
+    got, ro = gpu_knn(ctx, pairs)
+    for p, (i, j) in enumerate(pairs):
+        check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+
+
+def test_bunny_sift_all_pairs(ctx, golden_dir):
+    """Real SIFT descriptors of the 36 bunny images (52..500 per image)."""
+    z = np.load(golden_dir / "bunny_sift.npz")
+    off = z["offsets"]
+    descs = [z["desc"][off[i]:off[i + 1]] for i in range(len(off) - 1)]
+    register(ctx, descs)
+    n = len(descs)
+    pairs = np.array([(i, j) for i in range(n) for j in range(i + 1, n)], np.int32)
+    knn, ro = ctx.knn2(pairs)
+    mq, mt, md2, cnt = ctx.filter_matches(pairs, ro, knn)
+    torch.cuda.synchronize()
+    got = knn.cpu().numpy()
+    mq, mt, md2, cnt = (t.cpu().numpy() for t in (mq, mt, md2, cnt))
+    for p, (i, j) in enumerate(pairs):
+        check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+        q, t, d = oknn.match_features(descs[i], descs[j])
+        s = slice(int(ro[p]), int(ro[p]) + int(cnt[p]))
+        assert np.array_equal(mq[s], q) and np.array_equal(mt[s], t)
+        assert np.array_equal(np.sqrt(md2[s].astype(np.float32)), d)
+
+
+def test_mutual_nn_filter(ctx):
+    rng = np.random.default_rng(11)
+    d1 = rng.integers(0, 64, (300, 128)).astype(np.uint8)
+    d2 = rng.integers(0, 64, (700, 128)).astype(np.uint8)
+    d2[5] = d1[9]
+    d2[600] = d1[9]          # duplicate train rows: lowest index must win both ways
+    d1[17] = d1[9]
+    register(ctx, [d1, d2])
+    fwd, ro = ctx.knn2([(0, 1)])
+    rev, ro_rev = ctx.knn2([(1, 0)])
+    for ratio in (0.75, 2.0):            # 2.0 keeps every row: pure cross-check
+        mq, mt, md2, cnt = ctx.filter_matches([(0, 1)], ro, fwd, ratio, ro_rev, rev)
+        n = int(cnt.cpu()[0])
+        q, t, d = oknn.match_features(d1, d2, ratio=ratio, mutual=True)
+        assert np.array_equal(mq.cpu().numpy()[:n], q)
+        assert np.array_equal(mt.cpu().numpy()[:n], t)
+        assert np.array_equal(np.sqrt(md2.cpu().numpy()[:n].astype(np.float32)), d)
+
+
+def test_knn_8k_config_sample_vs_oracle_and_properties(ctx):
+    """BASELINE config 2 shape (8192-descriptor images): a sample of pairs against the
+    oracle, then size-independent properties on all pairs of the small set."""
+    from sfm_b200 import synth
+    s = synth.make_image_set(6, 8192, seed=synth.BASE_SEED + 1, device="cuda", tie_frac=0.01)
+    ctx.set_images(s.desc, s.kps, s.offsets.numpy())
+    n = 6
+    pairs = np.array([(i, j) for i in range(n) for j in range(n)], np.int32)
+    knn, ro = ctx.knn2(pairs)
+    knn2, _ = ctx.knn2(pairs)
+    torch.cuda.synchronize()
+    assert torch.equal(knn, knn2)                              # deterministic
+    got = knn.cpu().numpy().reshape(n, n, 8192, 4)
+    descs = [s.image(i)[0].cpu().numpy() for i in range(n)]
+    for (i, j) in [(0, 1), (1, 0), (2, 5), (4, 4)]:
+        check_pair(got[i, j], descs[i], descs[j])
+    assert np.all(got[..., 2] <= got[..., 3])                  # ascending distances
+    assert np.all(got[..., 0] != got[..., 1])
+    for i in range(n):                                         # self match: distance 0
+        assert np.all(got[i, i, :, 2] == 0)
+        assert np.all(got[i, i, :, 0] <= np.arange(8192))      # lowest index among duplicates
+    for i in range(n):                                         # min over rows == min over columns
+        for j in range(i + 1, n):
+            assert got[i, j, :, 2].min() == got[j, i, :, 2].min()

@@ -1,0 +1,176 @@
+"""GPU parity of K3 (RANSAC F) and K4 (geometric verification + quality gate)
+against the reference's golden artefacts (bunny_data/fundamental/*.npz packed
+into tests/golden/bunny_fundamental.npz together with the outputs of the
+reference's own ImageMatcher.geometric_verification / verify_match_quality).
+
+Tolerances for the RANSAC half are the ones calibrated in SURVEY.md 8c."""
+import numpy as np
+import pytest
+
+from oracle import fundamental as fm
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from sfm_b200 import lib as L
+    c = L.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def bunny(golden_dir):
+    return np.load(golden_dir / "bunny_fundamental.npz")
+
+
+def _dev(a, dtype):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype).cuda()
+
+
+def test_verification_given_reference_F(ctx, bunny):
+    """Same F in -> identical inlier masks, metrics within 1e-4, same gate decision
+    (reference utils/find_matches.py:157-214 on all 148 shipped pairs)."""
+    from sfm_b200 import lib as L
+    z = bunny
+    off = z["offsets"]
+    o = ctx.verify_given_F(off, _dev(z["pts1"], torch.float32), _dev(z["pts2"], torch.float32),
+                           _dev(z["F"].reshape(-1, 9), torch.float64))
+    torch.cuda.synchronize()
+    mask = o["mask"].cpu().numpy().astype(bool)
+    sym = o["sym"].cpu().numpy()
+    met = L.metrics_to_numpy(o["metrics"])
+    status = o["status"].cpu().numpy()
+    assert np.array_equal(mask, z["mask"])                       # 148/148 masks, 10,907 points
+    assert np.array_equal(sym.view(np.uint32), z["sym"].view(np.uint32))   # bitwise symmetric errors
+    g = z["metrics"]
+    assert np.array_equal(met["inliers"], g[:, 0].astype(np.int32))
+    assert np.array_equal(met["total_matches"], np.diff(off).astype(np.int32))
+    assert np.allclose(met["reprojection_error"], g[:, 2], rtol=1e-4, atol=0)
+    assert np.allclose(met["symmetric_error"], g[:, 3], rtol=1e-4, atol=0)
+    assert np.array_equal(met["well_distributed"].astype(bool), g[:, 4].astype(bool))
+    assert np.array_equal(status == L.PAIR_OK, z["passed"])
+
+
+def _ransac(ctx, z, **kw):
+    from sfm_b200 import lib as L
+    prm = L.default_params(**kw)
+    o = ctx.ransac_points(z["offsets"], _dev(z["pts1"], torch.float32), _dev(z["pts2"], torch.float32), prm)
+    torch.cuda.synchronize()
+    return (o["F"].cpu().numpy().reshape(-1, 3, 3), o["mask"].cpu().numpy().astype(bool),
+            L.metrics_to_numpy(o["metrics"]), o["status"].cpu().numpy())
+
+
+def test_ransac_vs_reference_golden(ctx, bunny):
+    from sfm_b200 import lib as L
+    z = bunny
+    off = z["offsets"]
+    F, mask, met, status = _ransac(ctx, z)
+    P = len(off) - 1
+    jac, dI, flips, errs, ref_errs = [], [], [], [], []
+    for k in range(P):
+        s = slice(int(off[k]), int(off[k + 1]))
+        M = s.stop - s.start
+        pts1, pts2 = z["pts1"][s], z["pts2"][s]
+        # the reference's own verification on OUR F (oracle restatement, pinned bitwise to cv2)
+        res = fm.geometric_verification(pts1, pts2, F[k])
+        assert np.array_equal(res["inlier_mask"], mask[s])       # K4 consistent with the oracle on new F
+        m_ref = z["mask"][s]
+        I_new, I_ref = int(mask[s].sum()), int(m_ref.sum())
+        # (1) one-sided inlier bound for every pair
+        assert I_new >= I_ref - max(3, 0.10 * M), (z["names"][k], I_new, I_ref, M)
+        inter = (mask[s] & m_ref).sum()
+        union = (mask[s] | m_ref).sum()
+        j = inter / union if union else 1.0
+        jac.append(j)
+        dI.append(I_new - I_ref)
+        if M >= 60:
+            assert j >= 0.85, (z["names"][k], j)
+        # (3) mean symmetric error over own inliers <= 2 px for every pair the reference passes
+        assert res["metrics"]["reprojection_error"] <= 2.0
+        errs.append(float(res["metrics"]["reprojection_error"]))
+        ref_errs.append(float(z["metrics"][k, 2]))
+        # (4) gate decision equal except gate-boundary pairs
+        ok_new = status[k] == L.PAIR_OK
+        if ok_new != bool(z["passed"][k]):
+            ref_res = fm.geometric_verification(pts1, pts2, z["F"][k])
+            in1 = pts1[ref_res["inlier_mask"]]
+            in2 = pts2[ref_res["inlier_mask"]]
+            min_std = min(in1.std(0).min(), in2.std(0).min())
+            boundary = I_ref <= 17 or min_std <= 21
+            assert boundary, (z["names"][k], I_ref, min_std)
+            flips.append(str(z["names"][k]))
+        # (5) rank 2, F[2,2] = 1
+        sv = np.linalg.svd(F[k], compute_uv=False)
+        assert sv[2] / sv[0] < 1e-6
+        assert abs(F[k][2, 2] - 1.0) < 1e-12 or abs(F[k][2, 2]) < 1e-6
+    jac = np.array(jac)
+    # (2) Jaccard distribution over the set
+    assert np.median(jac) >= 0.95, np.median(jac)
+    assert np.percentile(jac, 10) >= 0.85, np.percentile(jac, 10)
+    assert np.median(errs) <= np.median(ref_errs) * 1.05
+    assert len(flips) <= 8, flips
+    print(f"\nRANSAC parity: jaccard median {np.median(jac):.3f} p10 {np.percentile(jac, 10):.3f} "
+          f"min {jac.min():.3f}; dI median {np.median(dI):+.0f} min {min(dI):+d} max {max(dI):+d}; "
+          f"gate flips {flips}; err median {np.median(errs):.3f} (ref {np.median(ref_errs):.3f})")
+
+
+def test_ransac_is_deterministic_and_seeded(ctx, bunny):
+    F1, m1, _, s1 = _ransac(ctx, bunny)
+    F2, m2, _, s2 = _ransac(ctx, bunny)
+    assert np.array_equal(F1.view(np.uint64), F2.view(np.uint64))      # bit-identical under a fixed seed
+    assert np.array_equal(m1, m2) and np.array_equal(s1, s2)
+    F3, _, _, _ = _ransac(ctx, bunny, seed=12345)
+    assert not np.array_equal(F1, F3)                                   # the seed is live
+
+
+def test_ransac_gates(ctx):
+    """Skip reasons mirror utils/find_matches.py:274 / :284."""
+    from sfm_b200 import lib as L
+    rng = np.random.default_rng(0)
+    sizes = [0, 3, 4, 5, 7, 8, 40]
+    off = np.zeros(len(sizes) + 1, np.int64)
+    off[1:] = np.cumsum(sizes)
+    pts1 = (rng.random((off[-1], 2)) * 800).astype(np.float32)
+    pts2 = (rng.random((off[-1], 2)) * 800).astype(np.float32)
+    o = ctx.ransac_points(off, _dev(pts1, torch.float32), _dev(pts2, torch.float32))
+    torch.cuda.synchronize()
+    st = o["status"].cpu().numpy()
+    assert list(st[:5]) == [L.PAIR_TOO_FEW_MATCHES] * 3 + [L.PAIR_NO_MODEL] * 2
+    assert st[5] in (L.PAIR_QUALITY_FAIL, L.PAIR_NO_MODEL)
+    assert st[6] in (L.PAIR_QUALITY_FAIL, L.PAIR_NO_MODEL)     # random points never pass the gate
+    met = L.metrics_to_numpy(o["metrics"])
+    assert list(met["total_matches"]) == sizes
+
+
+def test_ransac_synthetic_two_view_geometry(ctx):
+    """Exact two-view geometry + outliers: the true inliers are recovered and the
+    estimated F explains them (large-M path: > 2048 correspondences are scored in chunks)."""
+    from sfm_b200 import lib as L
+    rng = np.random.default_rng(3)
+    M, n_out = 5000, 1500
+    X = rng.uniform([-7, -10, 20], [7, 10, 45], (M, 3))
+    K = np.array([[1228.0, 0, 512], [0, 1228.0, 384], [0, 0, 1]])
+    th = 0.2
+    R = np.array([[np.cos(th), 0, np.sin(th)], [0, 1, 0], [-np.sin(th), 0, np.cos(th)]])
+    t = np.array([3.0, 0.2, 0.5])
+    x1 = (K @ X.T).T
+    x2 = (K @ (R @ X.T + t[:, None])).T
+    p1 = (x1[:, :2] / x1[:, 2:]) + rng.normal(0, 0.3, (M, 2))
+    p2 = (x2[:, :2] / x2[:, 2:]) + rng.normal(0, 0.3, (M, 2))
+    out = rng.choice(M, n_out, replace=False)
+    p2[out] = rng.uniform([0, 0], [1024, 768], (n_out, 2))
+    off = np.array([0, M], np.int64)
+    o = ctx.ransac_points(off, _dev(p1, torch.float32), _dev(p2, torch.float32))
+    torch.cuda.synchronize()
+    mask = o["mask"].cpu().numpy().astype(bool)
+    truth = np.ones(M, bool)
+    truth[out] = False
+    assert (mask & truth).sum() >= 0.97 * truth.sum()
+    assert (mask & ~truth).sum() <= 0.12 * n_out       # random points within 3 px of an epipolar line
+    assert o["status"].cpu().numpy()[0] == L.PAIR_OK
+    F = o["F"].cpu().numpy().reshape(3, 3)
+    res = fm.geometric_verification(p1.astype(np.float32), p2.astype(np.float32), F)
+    assert np.array_equal(res["inlier_mask"], mask)
