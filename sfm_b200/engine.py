@@ -105,10 +105,14 @@ class PairEngine:
 
     # ----------------------------------------------------------- device path
     def match_device(self, pairs, only_ok: bool = True):
-        """Run K1..K4 + packing for one chunk; everything stays on the device.
-        Returns a dict of device tensors (views into reusable buffers)."""
-        torch, ctx = self.torch, self.ctx
+        """Run K1..K4 + packing for every chunk of the pair list; results stay on
+        the device.  Returns the list of per-chunk dicts."""
         pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
+        return [self._match_chunk(pairs[lo:hi], only_ok) for lo, hi in self._chunks(pairs)]
+
+    def _match_chunk(self, pairs, only_ok: bool = True):
+        """One chunk: dict of device tensors (the kNN / match arenas are reusable buffers)."""
+        torch, ctx = self.torch, self.ctx
         P = len(pairs)
         ro = ctx.query_rows(pairs)
         n = int(ro[-1])
@@ -136,7 +140,7 @@ class PairEngine:
         pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
         parts = []
         for lo, hi in self._chunks(pairs):
-            d = self.match_device(pairs[lo:hi], only_ok)
+            d = self._match_chunk(pairs[lo:hi], only_ok)
             total = int(d["pack_off"][-1].item())          # one sync per chunk
             nt_small = self.counts[pairs[lo:hi, 1]] < 2
             nq_zero = self.counts[pairs[lo:hi, 0]] < 1
