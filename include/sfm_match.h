@@ -190,10 +190,43 @@ SFM_API int64_t sfm_launch_count(sfm_ctx* ctx);
  * for `iters` 128x128x128 tile products per CTA and returns the elapsed
  * milliseconds (CUDA events) in *ms and the int8 op count in *ops. */
 SFM_API int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream);
+/* Same with 128 x tile_n x 128 tile products (tile_n = 64, 128 or 256; the peak probe uses 256):
+ * shows how the shared-memory operand reads of narrower tiles hold the tensor pipe back. */
+SFM_API int sfm_probe_int8_rate(sfm_ctx* ctx, int32_t iters, int32_t tile_n, float* ms, double* ops,
+                        void* stream);
 /* Debug: raw u8 x u8 dot products of one 128x128 tile pair through the same
  * TMA + tcgen05 path (rows q_row.. of the registered set against t_row..),
  * written to d_out i32 [128,128]. */
 SFM_API int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+
+/* Debug: the same tile with the fold step (see sfm_b200/csrc/knn.cu): accumulators
+ * a.b + 2016029 - floor(||b||^2 / 2) for query rows q_row.. against tile `tile` (128 rows) of
+ * `train_image`, written to d_out i32 [128,128]. */
+SFM_API int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_t tile,
+                        int32_t* d_out, void* stream);
+/* TMEM read-rate probe: every SM runs `warps` warps issuing `iters` tcgen05.ld each
+ * (variant 0: 32x32b.x32 + wait each; 1: .x32, wait every 4; 2: .x64 + wait each;
+ * 3: 16x256b.x8, wait every 4); *h_cycles = slowest warp's SM cycles (synchronises). */
+SFM_API int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant, int32_t iters,
+                            int64_t* h_cycles, void* stream);
+/* Issue-pattern probe: `steps` steps of 2 accumulators x k_per_acc 128x128x32 u8 MMAs on every
+ * SM, no data movement.  flags bit 0: commit per step; bit 1: consumer warps hand the TMEM stage
+ * back (needs bit 0 and consumers >= 1); bit 2: one extra commit per step.  *ms = elapsed. */
+SFM_API int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc, int32_t flags,
+                                  int32_t consumers, float* ms, void* stream);
+/* Select the kNN kernel variant used by sfm_knn2: 0 automatic (norm term folded
+ * into the contraction unless a registered row has ||b||^2 > 4,032,059, then the
+ * generic variant), 1 generic only, 2 folded only; timing probes whose output is NOT
+ * a kNN: 3 folded fast path only, 4 folded TMA + MMA pipeline without an epilogue. */
+SFM_API int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode);
+/* mbarrier suspend-time hints (ns; 0 = spin) of the kNN kernel's producer/MMA warps and of
+ * its epilogue warps.  Tuning knob; results do not depend on it. */
+SFM_API int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_wait_ns);
+/* Timing-probe switches of the kNN kernel (results become meaningless): bit 0 the producer
+ * skips the train-tile TMA loads, bit 1 the MMA warp skips the tcgen05.mma issue. */
+SFM_API int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags);
+/* Reads (synchronising `stream`) whether the registered set exceeded the fold range. */
+SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);
 
 #ifdef __cplusplus
 }

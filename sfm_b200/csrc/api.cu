@@ -54,11 +54,14 @@ struct sfm_ctx {
     int32_t n_images = 0;
     int64_t total_rows = 0;
     int64_t pad_total = 0;
-    std::vector<int64_t> h_off, h_pad;
-    CUtensorMap tmap;
+    std::vector<int64_t> h_off, h_pad, h_x;
+    CUtensorMap tmap, tmap_x;
     bool have_tmap = false;
-    DevBuf<int64_t> d_img_off, d_pad_off;
-    DevBuf<int32_t> d_norms, d_norms_pad;
+    DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
+    DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
+    DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
+    int knn_mode = 0;            // sfm_debug_set_knn_mode
+    sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
     DevBuf<int32_t> d_pairs;
@@ -200,6 +203,9 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_pad_off.release();
     ctx->d_norms.release();
     ctx->d_norms_pad.release();
+    ctx->d_x_off.release();
+    ctx->d_flags.release();
+    ctx->d_bias.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
     ctx->d_work.release();
@@ -235,11 +241,25 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     }
     ctx->pad_total = ctx->h_pad[n_images];
     if (ctx->pad_total >= (int64_t(1) << 31)) return ctx->fail("padded column space too large");
+    // fold-step bias rows: 128 constant rows, then 128 rows per 512 train rows of each image
+    ctx->h_x.resize(n_images + 1);
+    ctx->h_x[0] = SFM_TTILE;
+    for (int i = 0; i < n_images; ++i) {
+        const int64_t n = h_offsets[i + 1] - h_offsets[i];
+        ctx->h_x[i + 1] = ctx->h_x[i] + (n + 4 * SFM_TTILE - 1) / (4 * SFM_TTILE) * SFM_TTILE;
+    }
+    const int64_t x_rows = ctx->h_x[n_images];
+    if (x_rows >= (int64_t(1) << 31)) return ctx->fail("bias row space too large");
 
     SFM_CUDA(ctx, ctx->d_img_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_pad_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_norms.reserve(static_cast<size_t>(total) + 1));
     SFM_CUDA(ctx, ctx->d_norms_pad.reserve(static_cast<size_t>(ctx->pad_total) + 4));
+    SFM_CUDA(ctx, ctx->d_x_off.reserve(n_images + 1));
+    SFM_CUDA(ctx, ctx->d_flags.reserve(4));
+    SFM_CUDA(ctx, ctx->d_bias.reserve(static_cast<size_t>(x_rows) * SFM_DESC_DIM));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_x_off.p, ctx->h_x.data(), sizeof(int64_t) * (n_images + 1),
+                                  cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
                                   cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_pad_off.p, ctx->h_pad.data(), sizeof(int64_t) * (n_images + 1),
@@ -256,10 +276,15 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled failed: CUresult %d", int(r));
+        const cuuint64_t xdim[2] = {SFM_DESC_DIM, static_cast<cuuint64_t>(x_rows)};
+        r = ctx->encode(&ctx->tmap_x, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_bias.p, xdim, gstride, box,
+                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (bias) failed: CUresult %d", int(r));
         ctx->have_tmap = true;
     }
-    sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, n_images, ctx->pad_total,
-                      ctx->d_norms.p, ctx->d_norms_pad.p, st, &ctx->launches);
+    sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, ctx->d_x_off.p, n_images,
+                      ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_bias.p, ctx->d_flags.p, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     return 0;
 }
@@ -290,9 +315,10 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
         return 1;
     SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
     sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
-                           ctx->d_work.p, st, &ctx->launches);
-    int r = sfm::launch_knn2(ctx->tmap, ctx->d_work.p, n_work, ctx->d_norms.p, ctx->d_norms_pad.p, d_knn,
-                             ctx->num_sms, st, &ctx->launches);
+                           ctx->d_x_off.p, ctx->d_work.p, st, &ctx->launches);
+    int r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_work.p, n_work, ctx->d_norms.p,
+                             ctx->d_norms_pad.p, ctx->d_flags.p, ctx->knn_mode, ctx->knn_tuning, d_knn, ctx->num_sms, st,
+                             &ctx->launches);
     if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     return 0;
 }
@@ -417,17 +443,22 @@ int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row_off, co
 }
 
 int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream) {
+    return sfm_probe_int8_rate(ctx, iters, 256, ms, ops, stream);
+}
+
+int sfm_probe_int8_rate(sfm_ctx* ctx, int32_t iters, int32_t tile_n, float* ms, double* ops, void* stream) {
     if (!ctx) return 1;
     if (iters <= 0 || !ms || !ops) return ctx->fail("bad probe arguments");
+    if (tile_n != 64 && tile_n != 128 && tile_n != 256) return ctx->fail("tile_n must be 64, 128 or 256");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaEvent_t e0, e1;
     SFM_CUDA(ctx, cudaEventCreate(&e0));
     SFM_CUDA(ctx, cudaEventCreate(&e1));
-    int r = sfm::launch_mma_probe(iters, ctx->num_sms, st, &ctx->launches);   // warm-up
+    int r = sfm::launch_mma_probe(iters, tile_n, ctx->num_sms, st, &ctx->launches);   // warm-up
     if (!r) {
         cudaEventRecord(e0, st);
-        r = sfm::launch_mma_probe(iters, ctx->num_sms, st, &ctx->launches);
+        r = sfm::launch_mma_probe(iters, tile_n, ctx->num_sms, st, &ctx->launches);
         cudaEventRecord(e1, st);
     }
     cudaError_t e = cudaEventSynchronize(e1);
@@ -439,7 +470,7 @@ int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, voi
     cudaEventElapsedTime(ms, e0, e1);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
-    *ops = 2.0 * 128.0 * 256.0 * 128.0 * static_cast<double>(iters) * ctx->num_sms;
+    *ops = 2.0 * 128.0 * tile_n * 128.0 * static_cast<double>(iters) * ctx->num_sms;
     return 0;
 }
 
@@ -448,9 +479,106 @@ int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_ou
     if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
     if (!d_out) return ctx->fail("d_out is NULL");
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
-    int r = sfm::launch_debug_dot(ctx->tmap, static_cast<int32_t>(q_row), static_cast<int32_t>(t_row),
-                                  d_out, static_cast<cudaStream_t>(stream), &ctx->launches);
+    int r = sfm::launch_debug_dot(ctx->tmap, ctx->tmap_x, static_cast<int32_t>(q_row),
+                                  static_cast<int32_t>(t_row), -1, 0, d_out,
+                                  static_cast<cudaStream_t>(stream), &ctx->launches);
     if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_t tile, int32_t* d_out,
+                        void* stream) {
+    if (!ctx) return 1;
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
+    if (!d_out) return ctx->fail("d_out is NULL");
+    if (train_image < 0 || train_image >= ctx->n_images) return ctx->fail("train image out of range");
+    const int64_t n = ctx->h_off[train_image + 1] - ctx->h_off[train_image];
+    if (tile < 0 || int64_t(tile) * SFM_TTILE >= n) return ctx->fail("tile out of range");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t t_row = ctx->h_off[train_image] + int64_t(tile) * SFM_TTILE;
+    const int64_t x_row = ctx->h_x[train_image] + int64_t(tile / 4) * SFM_TTILE;
+    int r = sfm::launch_debug_dot(ctx->tmap, ctx->tmap_x, static_cast<int32_t>(q_row),
+                                  static_cast<int32_t>(t_row), static_cast<int32_t>(x_row), tile % 4, d_out,
+                                  static_cast<cudaStream_t>(stream), &ctx->launches);
+    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant, int32_t iters, int64_t* h_cycles,
+                            void* stream) {
+    if (!ctx) return 1;
+    if (warps < 1 || warps > 16 || variant < 0 || variant > 3 || iters < 1 || !h_cycles)
+        return ctx->fail("bad probe arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n = static_cast<size_t>(ctx->num_sms) * warps;
+    SFM_CUDA(ctx, ctx->d_meta.reserve(n));
+    int r = sfm::launch_tmem_ld_probe(warps, variant, iters, ctx->num_sms,
+                                      reinterpret_cast<long long*>(ctx->d_meta.p), st, &ctx->launches);
+    if (r) return ctx->fail("probe launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    std::vector<int64_t> h(n);
+    SFM_CUDA(ctx, cudaMemcpyAsync(h.data(), ctx->d_meta.p, n * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA(ctx, cudaStreamSynchronize(st));
+    int64_t mx = 0;
+    for (int64_t c : h) mx = c > mx ? c : mx;
+    *h_cycles = mx;
+    return 0;
+}
+
+int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc, int32_t flags,
+                                  int32_t consumers, float* ms, void* stream) {
+    if (!ctx) return 1;
+    if (steps < 1 || k_per_acc < 1 || k_per_acc > 8 || consumers < 0 || consumers > 9 || !ms)
+        return ctx->fail("bad probe arguments");
+    if ((flags & 2) && (!(flags & 1) || consumers < 1)) return ctx->fail("hand-shake needs commits and consumers");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1;
+    SFM_CUDA(ctx, cudaEventCreate(&e0));
+    SFM_CUDA(ctx, cudaEventCreate(&e1));
+    int r = sfm::launch_mma_handshake_probe(steps, k_per_acc, flags, consumers, ctx->num_sms, st, &ctx->launches);
+    if (!r) {
+        cudaEventRecord(e0, st);
+        r = sfm::launch_mma_handshake_probe(steps, k_per_acc, flags, consumers, ctx->num_sms, st, &ctx->launches);
+        cudaEventRecord(e1, st);
+    }
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (!r && e == cudaSuccess) cudaEventElapsedTime(ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (r || e != cudaSuccess)
+        return ctx->fail("probe failed: %s", cudaGetErrorString(r ? static_cast<cudaError_t>(r) : e));
+    return 0;
+}
+
+int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
+    if (!ctx) return 1;
+    if (mode < 0 || mode > 4) return ctx->fail("knn mode must be 0..4");
+    ctx->knn_mode = mode;
+    return 0;
+}
+
+int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags) {
+    if (!ctx) return 1;
+    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 3u;
+    return 0;
+}
+
+int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_wait_ns) {
+    if (!ctx) return 1;
+    if (wait_ns < 0 || epi_wait_ns < 0) return ctx->fail("wait hints must be >= 0");
+    ctx->knn_tuning.wait_ns = static_cast<uint32_t>(wait_ns);
+    ctx->knn_tuning.epi_wait_ns = static_cast<uint32_t>(epi_wait_ns);
+    return 0;
+}
+
+int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream) {
+    if (!ctx || !h_flag) return 1;
+    if (!ctx->d_flags.p) return ctx->fail("no descriptors registered");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_flag, ctx->d_flags.p, sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                  static_cast<cudaStream_t>(stream)));
+    SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
     return 0;
 }
 

@@ -16,24 +16,39 @@ struct __align__(16) WorkItem {
     int32_t t_row;    // first row of the train image
     int32_t t_cnt;    // rows of the train image
     int32_t t_pad;    // offset of the train image in the 128-padded column-norm array
-    int32_t reserved;
+    int32_t x_row;    // first row of the train image in the fold-step bias array (128-byte rows)
     int64_t out_row;  // first output row of this block in d_knn
 };
 static_assert(sizeof(WorkItem) == 32, "WorkItem must be 32 bytes");
 
-// ---- norms.cu / knn.cu
+// ---- knn.cu
+// Bias array of the fold step: 128-byte rows; rows [0,128) are the constant A operand,
+// image i owns rows [x_off[i], x_off[i+1]) = 128 * ceil(n_i / 512).
 void launch_norms(const uint8_t* d_desc, int64_t total_rows, const int64_t* d_img_off,
-                  const int64_t* d_pad_off, int32_t n_images, int64_t pad_total, int32_t* d_norms,
-                  int32_t* d_norms_pad, cudaStream_t st, int64_t* launches);
+                  const int64_t* d_pad_off, const int64_t* d_x_off, int32_t n_images,
+                  int32_t* d_norms, int32_t* d_norms_pad, uint8_t* d_bias, int32_t* d_flags,
+                  cudaStream_t st, int64_t* launches);
 void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_blk_prefix,
                        const int64_t* d_row_off, const int64_t* d_img_off, const int64_t* d_pad_off,
-                       WorkItem* d_work, cudaStream_t st, int64_t* launches);
-int launch_knn2(const CUtensorMap& tmap, const WorkItem* d_work, int64_t n_work,
-                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_knn, int num_sms,
-                cudaStream_t st, int64_t* launches);
-int launch_debug_dot(const CUtensorMap& tmap, int32_t q_row, int32_t t_row, int32_t* d_out,
-                     cudaStream_t st, int64_t* launches);
-int launch_mma_probe(int32_t iters, int num_sms, cudaStream_t st, int64_t* launches);
+                       const int64_t* d_x_off, WorkItem* d_work, cudaStream_t st, int64_t* launches);
+struct KnnTuning {
+    uint32_t wait_ns = 2000;      // mbarrier suspend hint of the producer / MMA warps (0 = spin)
+    uint32_t epi_wait_ns = 200;   // same for the epilogue warps' accumulator-ready wait
+    uint32_t probe_flags = 0;     // timing probes: bit 0 no B-tile TMA traffic, bit 1 no MMA issue
+};
+int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work, int64_t n_work,
+                const int32_t* d_norms, const int32_t* d_norms_pad, const int32_t* d_flags, int mode,
+                const KnnTuning& tn, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
+int launch_debug_dot(const CUtensorMap& tmap, const CUtensorMap& tmap_x, int32_t q_row, int32_t t_row,
+                     int32_t x_row, int32_t x_chunk, int32_t* d_out, cudaStream_t st, int64_t* launches);
+int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t st, int64_t* launches);
+
+// ---- probes.cu
+int launch_tmem_ld_probe(int warps, int variant, int iters, int num_sms, long long* d_out, cudaStream_t st,
+                         int64_t* launches);
+
+int launch_mma_handshake_probe(int steps, int k_per_acc, int flags, int consumers, int num_sms,
+                               cudaStream_t st, int64_t* launches);
 
 // ---- filter.cu
 void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,

@@ -3,9 +3,9 @@
 // Replaces cv2.BFMatcher(NORM_L2).knnMatch(desc1, desc2, k=2)
 // (reference utils/find_matches.py:144-147).  SIFT descriptors are integers
 // 0..255, so ||a-b||^2 = ||a||^2 + ||b||^2 - 2 a.b is computed exactly:
-// a.b as u8 x u8 -> s32 tcgen05.mma tiles accumulated in TMEM, the norms by a
-// small dp4a kernel.  The top-2 selection is fused into the TMEM epilogue, so
-// the distance matrix never reaches HBM.
+// a.b as u8 x u8 -> s32 tcgen05.mma tiles accumulated in TMEM.  The top-2
+// selection is fused into the TMEM epilogue, so the distance matrix never
+// reaches HBM.
 //
 // One persistent CTA per SM, warp-specialised:
 //   warps 0-7  epilogue: thread <-> one query row (TMEM lane); running
@@ -16,9 +16,25 @@
 // accumulators of a train tile form one TMEM stage (256 columns), two stages
 // are in flight so the epilogue of tile t overlaps the MMAs of tile t+1.
 //
+// K = 128 is so short that the epilogue (16384 accumulators per 270-cycle
+// tile) is the bound, not the tensor pipe.  Two kernel variants:
+//
+//  kFold (default): the column-norm term is folded INTO the contraction.  A
+//    fifth K-step multiplies a constant u8 row (1, 255 x 31) with a per-train-
+//    row u8 row holding the digits of C - floor(||b||^2 / 2), C = 2,016,029, so
+//    the accumulator already holds v = a.b + C - floor(||b||^2/2) and the exact
+//    ranking key is 2(v - C) - (||b||^2 & 1) = 2 a.b - ||b||^2 (maximise;
+//    d^2 = ||a||^2 - key).  All five K-steps share one instruction descriptor
+//    (u8 x u8).  The epilogue is then a max3 tree (0.6 instr/element) compared
+//    against a per-row threshold; only 4-column groups that can change the
+//    top-2 are looked at exactly.  Needs ||b||^2 <= 4,032,059 (norm <= 2008;
+//    SIFT is 512); sfm_set_images raises a device flag otherwise and the
+//    generic variant runs instead.
+//  kGeneric: keys computed per element from a padded column-norm array.
+//
 // Tie rule (== OpenCV): columns are visited in ascending train
-// index and a candidate replaces an incumbent only on strict '<', so the
-// lowest index wins ties for both the best and the second best.
+// index and a candidate replaces an incumbent only on strict comparison, so
+// the lowest index wins ties for both the best and the second best.
 #include <climits>
 
 #include "kernels.h"
@@ -36,6 +52,8 @@ constexpr int kTileBytes = kTileM * kRowBytes;      // 16 KiB (A tile == B tile)
 constexpr int kABlockBytes = kATiles * kTileBytes;  // 32 KiB
 constexpr int kAStages = 2;
 constexpr int kBStages = 6;
+constexpr int kXStages = 2;                          // bias tiles (one per 4 train tiles)
+constexpr int kXGroup = 4;                           // train tiles per bias tile
 constexpr int kTmemStages = 2;
 constexpr int kTmemColsPerStage = kATiles * kTileN;  // 256
 constexpr int kTmemCols = kTmemStages * kTmemColsPerStage;  // 512 = all of TMEM
@@ -47,10 +65,17 @@ constexpr int kUmmaK = 32;                           // bytes of K per tcgen05.m
 constexpr int kKSteps = kRowBytes / kUmmaK;          // 4
 constexpr uint32_t kIdesc = make_idesc_u8(kTileM, kTileN);
 constexpr int kPadNorm = 1 << 30;                    // column norm of a padding column
+constexpr int kNegV = -(1 << 28);                    // folded accumulator of a masked column (2v - 2C must not wrap)
+// fold constant C: the largest value the 32 u8 bias digits (weights 1, 255 x 31) can express
+constexpr int kFoldC = 255 * 31 * 255 + 254;
 
-constexpr size_t kSmemData = size_t(kAStages) * kABlockBytes + size_t(kBStages) * kTileBytes;
-constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 2 * kTmemStages;
+enum KnnMode { kGeneric = 0, kFold = 1, kFoldFastOnly = 2, kFoldNoEpilogue = 3 };
+
+constexpr size_t kSmemData = size_t(kAStages) * kABlockBytes + size_t(kBStages) * kTileBytes +
+                             size_t(kXStages + 1) * kTileBytes;
+constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 2 * kTmemStages + 2 * kXStages + 1;
 constexpr size_t kSmemBytes = kSmemData + kNumBars * 8 + 16 + 1024;  // + alignment slack
+static_assert(kSmemBytes <= 232448, "shared memory budget");
 
 struct Pipe {
     int stage = 0;
@@ -65,6 +90,7 @@ struct Pipe {
     }
 };
 
+// ------------------------------------------------------------------ generic epilogue
 struct Top2 {
     int d1, d2, i1, i2;
 };
@@ -109,21 +135,90 @@ __device__ __forceinline__ void top2_chunk(Top2& s, const uint32_t (&acc)[32], c
     }
 }
 
+// ------------------------------------------------------------------ folded epilogue
+// Running top-2 of the exact key K = 2 a.b - ||b||^2 = 2 (v - C) - p (maximised), p the
+// parity of ||b||^2.  `thr` is the smallest folded accumulator v that can still enter:
+// 2 (v - C) - p > k2 for some p in {0,1}  <=>  v >= (k2 >> 1) + 1 + C.
+struct Top2K {
+    int k1, k2, i1, i2, thr;
+};
+
+__device__ __forceinline__ void top2k_insert(Top2K& s, int key, int col) {
+    if (key > s.k2) {
+        if (key > s.k1) {
+            s.k2 = s.k1;
+            s.i2 = s.i1;
+            s.k1 = key;
+            s.i1 = col;
+        } else {
+            s.k2 = key;
+            s.i2 = col;
+        }
+        s.thr = (s.k2 >> 1) + 1 + kFoldC;
+    }
+}
+
+// 32 folded accumulators of one row.  `nbp` points at the padded column norms
+// of column col0 (only read on the exact path, for the parity bit).  MASKED:
+// columns >= t_cnt (last, partial train tile) are forced out.
+template <bool MASKED, int MODE>
+__device__ __forceinline__ void fold_chunk(Top2K& s, const uint32_t (&acc)[32],
+                                           const int32_t* __restrict__ nbp, int col0, int t_cnt) {
+    int v[32];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        v[e] = static_cast<int>(acc[e]);
+        if (MASKED) v[e] = (col0 + e < t_cnt) ? v[e] : kNegV;
+    }
+    int m4[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        m4[j] = max(__vimax3_s32(v[4 * j], v[4 * j + 1], v[4 * j + 2]), v[4 * j + 3]);
+    const int m = max(__vimax3_s32(__vimax3_s32(m4[0], m4[1], m4[2]), __vimax3_s32(m4[3], m4[4], m4[5]),
+                                   m4[6]),
+                      m4[7]);
+    if (MODE == kFoldFastOnly) {
+        s.k1 = max(s.k1, m);   // timing probe: fast path only (results are not a kNN)
+        return;
+    }
+    if (m >= s.thr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (m4[j] >= s.thr) {
+                const int4 nb = __ldg(reinterpret_cast<const int4*>(nbp) + j);
+                const int c = col0 + 4 * j;
+                const int p4[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (!MASKED || c + e < t_cnt)   // masked columns never enter, whatever the state
+                        top2k_insert(s, 2 * v[4 * j + e] - (p4[e] + 2 * kFoldC), c + e);
+            }
+        }
+    }
+}
+
 struct SmemLayout {
     uint8_t* a;
     uint8_t* b;
+    uint8_t* x;    // kXStages bias tiles
+    uint8_t* ax;   // constant A operand of the fold step
     uint64_t* a_full;
     uint64_t* a_empty;
     uint64_t* b_full;
     uint64_t* b_empty;
     uint64_t* t_full;
     uint64_t* t_empty;
+    uint64_t* x_full;
+    uint64_t* x_empty;
+    uint64_t* ax_full;
     uint32_t* tmem_slot;
     __device__ explicit SmemLayout(uint8_t* raw) {
         uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) &
                                                    ~static_cast<uintptr_t>(1023));
         a = base;
-        b = base + size_t(kAStages) * kABlockBytes;
+        b = a + size_t(kAStages) * kABlockBytes;
+        x = b + size_t(kBStages) * kTileBytes;
+        ax = x + size_t(kXStages) * kTileBytes;
         uint64_t* bars = reinterpret_cast<uint64_t*>(base + kSmemData);
         a_full = bars;
         a_empty = a_full + kAStages;
@@ -131,14 +226,25 @@ struct SmemLayout {
         b_empty = b_full + kBStages;
         t_full = b_empty + kBStages;
         t_empty = t_full + kTmemStages;
-        tmem_slot = reinterpret_cast<uint32_t*>(t_empty + kTmemStages);
+        x_full = t_empty + kTmemStages;
+        x_empty = x_full + kXStages;
+        ax_full = x_empty + kXStages;
+        tmem_slot = reinterpret_cast<uint32_t*>(ax_full + 1);
     }
 };
 
+// `flags[0]` != 0: some registered row's norm is beyond what the fold step can
+// encode -> only the generic variant may run.  Both variants are launched
+// back to back (no host synchronisation); the one that does not apply exits.
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
-knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict__ work,
-            long long n_work, const int32_t* __restrict__ norms,
-            const int32_t* __restrict__ norms_pad, int4* __restrict__ out) {
+knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
+            const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms,
+            const int32_t* __restrict__ norms_pad, const int32_t* __restrict__ flags, int force,
+            uint32_t wait_ns, uint32_t epi_wait_ns, uint32_t probe_flags, int4* __restrict__ out) {
+    constexpr bool FOLD = MODE != kGeneric;
+    if (!force && ((__ldg(flags) != 0) == FOLD)) return;
+
     extern __shared__ uint8_t smem_raw[];
     SmemLayout sm(smem_raw);
     const int warp = threadIdx.x >> 5;
@@ -146,6 +252,7 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
 
     if (warp == kProducerWarp && lane == 0) {
         tma_prefetch_desc(&tmap);
+        if (FOLD) tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < kAStages; ++i) {
             mbar_init(&sm.a_full[i], 1);
             mbar_init(&sm.a_empty[i], 1);
@@ -158,6 +265,11 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
             mbar_init(&sm.t_full[i], 1);
             mbar_init(&sm.t_empty[i], kEpiWarps);
         }
+        for (int i = 0; i < kXStages; ++i) {
+            mbar_init(&sm.x_full[i], 1);
+            mbar_init(&sm.x_empty[i], 1);
+        }
+        mbar_init(sm.ax_full, 1);
         fence_barrier_init();
     }
     if (warp == kMmaWarp) {
@@ -169,63 +281,109 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
     tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_slot;
 
+    // Producer and MMA warps run their loops warp-convergent (all 32 lanes wait and keep the
+    // pipeline state) and only the TMA / tcgen05 issue is predicated on one elected lane: the
+    // descriptors then live in uniform registers and each tcgen05.mma is a single predicated
+    // instruction.  (Under `if (lane == 0)` ptxas wraps every UTCIMMA in an R2UR + elect loop
+    // and the issuing thread, not the tensor pipe, paces the kernel.)
     if (warp == kProducerWarp) {
-        if (lane == 0) {
-            Pipe ap(kAStages), bp(kBStages);
-            for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
-                const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
-                const int q_row = w0.x, t_row = w0.z, t_cnt = w0.w;
-                mbar_wait(&sm.a_empty[ap.stage], ap.phase ^ 1);
+        Pipe ap(kAStages), bp(kBStages), xp(kXStages);
+        if (FOLD && elect_one()) {   // constant A operand of the fold step: rows 0..127 of the bias array
+            mbar_arrive_expect_tx(sm.ax_full, kTileBytes);
+            tma_load_2d(sm.ax, &tmap_x, sm.ax_full, 0, 0);
+        }
+        __syncwarp();
+        for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
+            const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
+            const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
+            const int q_row = w0.x, t_row = w0.z, t_cnt = w0.w, x_row = w1.y;
+            mbar_wait_suspend(&sm.a_empty[ap.stage], ap.phase ^ 1, wait_ns);
+            if (elect_one()) {
                 mbar_arrive_expect_tx(&sm.a_full[ap.stage], kABlockBytes);
                 uint8_t* a_dst = sm.a + size_t(ap.stage) * kABlockBytes;
 #pragma unroll
                 for (int a = 0; a < kATiles; ++a)
-                    tma_load_2d(a_dst + a * kTileBytes, &tmap, &sm.a_full[ap.stage], 0,
-                                q_row + a * kTileM);
-                ap.advance();
-                const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
-                for (int t = 0; t < n_tiles; ++t) {
-                    mbar_wait(&sm.b_empty[bp.stage], bp.phase ^ 1);
-                    mbar_arrive_expect_tx(&sm.b_full[bp.stage], kTileBytes);
-                    tma_load_2d(sm.b + size_t(bp.stage) * kTileBytes, &tmap, &sm.b_full[bp.stage], 0,
-                                t_row + t * kTileN);
-                    bp.advance();
+                    tma_load_2d(a_dst + a * kTileBytes, &tmap, &sm.a_full[ap.stage], 0, q_row + a * kTileM);
+            }
+            __syncwarp();
+            ap.advance();
+            const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
+            for (int t = 0; t < n_tiles; ++t) {
+                if (FOLD && (t % kXGroup) == 0) {
+                    mbar_wait_suspend(&sm.x_empty[xp.stage], xp.phase ^ 1, wait_ns);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&sm.x_full[xp.stage], kTileBytes);
+                        tma_load_2d(sm.x + size_t(xp.stage) * kTileBytes, &tmap_x, &sm.x_full[xp.stage], 0,
+                                    x_row + (t / kXGroup) * kTileM);
+                    }
+                    __syncwarp();
+                    xp.advance();
                 }
+                mbar_wait_suspend(&sm.b_empty[bp.stage], bp.phase ^ 1, wait_ns);
+                if (elect_one()) {
+                    if (probe_flags & 1u) {   // probe: no B traffic
+                        mbar_arrive(&sm.b_full[bp.stage]);
+                    } else {
+                        mbar_arrive_expect_tx(&sm.b_full[bp.stage], kTileBytes);
+                        tma_load_2d(sm.b + size_t(bp.stage) * kTileBytes, &tmap, &sm.b_full[bp.stage], 0,
+                                    t_row + t * kTileN);
+                    }
+                }
+                __syncwarp();
+                bp.advance();
             }
         }
     } else if (warp == kMmaWarp) {
-        if (lane == 0) {
-            Pipe ap(kAStages), bp(kBStages), tp(kTmemStages);
-            for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
-                const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
-                const int n_tiles = (w0.w + kTileN - 1) / kTileN;
-                mbar_wait(&sm.a_full[ap.stage], ap.phase);
+        Pipe ap(kAStages), bp(kBStages), tp(kTmemStages), xp(kXStages);
+        uint64_t axdesc = 0;
+        if (FOLD) {
+            mbar_wait_suspend(sm.ax_full, 0, wait_ns);
+            axdesc = make_kmajor_sw128_desc(smem_u32(sm.ax));
+        }
+        for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
+            const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
+            const int n_tiles = (w0.w + kTileN - 1) / kTileN;
+            mbar_wait_suspend(&sm.a_full[ap.stage], ap.phase, wait_ns);
+            const uint64_t adesc0 = make_kmajor_sw128_desc(smem_u32(sm.a + size_t(ap.stage) * kABlockBytes));
+            uint64_t xdesc0 = 0;
+            for (int t = 0; t < n_tiles; ++t) {
+                if (FOLD && (t % kXGroup) == 0) {
+                    mbar_wait_suspend(&sm.x_full[xp.stage], xp.phase, wait_ns);
+                    xdesc0 = make_kmajor_sw128_desc(smem_u32(sm.x + size_t(xp.stage) * kTileBytes));
+                }
+                mbar_wait_suspend(&sm.t_empty[tp.stage], tp.phase ^ 1, wait_ns);
+                mbar_wait_suspend(&sm.b_full[bp.stage], bp.phase, wait_ns);
                 tc_fence_after();
-                const uint64_t adesc0 =
-                    make_kmajor_sw128_desc(smem_u32(sm.a + size_t(ap.stage) * kABlockBytes));
-                for (int t = 0; t < n_tiles; ++t) {
-                    mbar_wait(&sm.t_empty[tp.stage], tp.phase ^ 1);
-                    mbar_wait(&sm.b_full[bp.stage], bp.phase);
-                    tc_fence_after();
-                    const uint64_t bdesc0 =
-                        make_kmajor_sw128_desc(smem_u32(sm.b + size_t(bp.stage) * kTileBytes));
+                const uint64_t bdesc0 = make_kmajor_sw128_desc(smem_u32(sm.b + size_t(bp.stage) * kTileBytes));
+                const uint64_t xdesc = xdesc0 + uint64_t(t % kXGroup) * (kUmmaK >> 4);
+                const uint32_t d0 = tmem_base + tp.stage * kTmemColsPerStage;
+                const bool x_done = FOLD && ((t % kXGroup) == kXGroup - 1 || t == n_tiles - 1);
+                if (elect_one()) {
+                    if (!(probe_flags & 2u)) {   // (probe bit 1: no MMA issue)
 #pragma unroll
-                    for (int a = 0; a < kATiles; ++a) {
-                        const uint32_t d = tmem_base + tp.stage * kTmemColsPerStage + a * kTileN;
-                        const uint64_t adesc = adesc0 + uint64_t(a) * (kTileBytes >> 4);
+                        for (int a = 0; a < kATiles; ++a) {
+                            const uint32_t d = d0 + a * kTileN;
+                            const uint64_t adesc = adesc0 + uint64_t(a) * (kTileBytes >> 4);
 #pragma unroll
-                        for (int k = 0; k < kKSteps; ++k)
-                            mma_i8_ss(d, adesc + uint64_t(k) * (kUmmaK >> 4),
-                                      bdesc0 + uint64_t(k) * (kUmmaK >> 4), kIdesc, k > 0);
+                            for (int k = 0; k < kKSteps; ++k)
+                                mma_i8_ss(d, adesc + uint64_t(k) * (kUmmaK >> 4),
+                                          bdesc0 + uint64_t(k) * (kUmmaK >> 4), kIdesc, k > 0);
+                            if (FOLD)   // + (1, 255 x 31) . digits(C - floor(||b||^2 / 2))
+                                mma_i8_ss(d, axdesc, xdesc, kIdesc, 1);
+                        }
                     }
                     mma_commit(&sm.b_empty[bp.stage]);   // B slot reusable once the MMAs retire
                     mma_commit(&sm.t_full[tp.stage]);    // accumulators ready for the epilogue
-                    bp.advance();
-                    tp.advance();
+                    if (x_done) mma_commit(&sm.x_empty[xp.stage]);
                 }
-                mma_commit(&sm.a_empty[ap.stage]);
-                ap.advance();
+                __syncwarp();
+                if (x_done) xp.advance();
+                bp.advance();
+                tp.advance();
             }
+            if (elect_one()) mma_commit(&sm.a_empty[ap.stage]);
+            __syncwarp();
+            ap.advance();
         }
     } else {
         // ------------------------------------------------ epilogue warps
@@ -242,20 +400,33 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
                 static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
             const bool valid = row < q_cnt;
             const int na = valid ? __ldg(norms + q_row + row) : 0;
-            Top2 s{INT_MAX, INT_MAX, -1, -1};
             const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
-            const int4* nbp = reinterpret_cast<const int4*>(norms_pad + t_pad);
+            const int32_t* nbase = norms_pad + t_pad;
+            Top2 s{INT_MAX, INT_MAX, -1, -1};
+            Top2K sk{INT_MIN, INT_MIN, -1, -1, (INT_MIN >> 1) + 1 + kFoldC};
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait(&sm.t_full[tp.stage], tp.phase);
+                mbar_wait_suspend(&sm.t_full[tp.stage], tp.phase, epi_wait_ns);
                 tc_fence_after();
                 const uint32_t taddr = lane_addr + tp.stage * kTmemColsPerStage;
+                if (MODE == kFoldNoEpilogue) {   // timing probe: TMA + MMA pipeline alone
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.t_empty[tp.stage]);
+                    tp.advance();
+                    continue;
+                }
+                const bool partial = FOLD && (t + 1) * kTileN > t_cnt;
                 uint32_t v[2][32];
                 tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
                 for (int c = 0; c < kTileN / 32; ++c) {
+                    const int col0 = t * kTileN + c * 32;
                     int4 nb[8];
+                    if (!FOLD) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) nb[j] = __ldg(nbp + (t * kTileN + c * 32) / 4 + j);
+                        for (int j = 0; j < 8; ++j)
+                            nb[j] = __ldg(reinterpret_cast<const int4*>(nbase) + col0 / 4 + j);
+                    }
                     tmem_ld_wait();
                     if (c + 1 < kTileN / 32) {
                         tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
@@ -265,17 +436,31 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&sm.t_empty[tp.stage]);
                     }
-                    top2_chunk(s, v[c & 1], nb, t * kTileN + c * 32);
+                    if (!FOLD) {
+                        top2_chunk(s, v[c & 1], nb, col0);
+                    } else if (partial) {
+                        fold_chunk<true, MODE>(sk, v[c & 1], nbase + col0, col0, t_cnt);
+                    } else {
+                        fold_chunk<false, MODE>(sk, v[c & 1], nbase + col0, col0, t_cnt);
+                    }
                 }
                 tp.advance();
             }
             if (valid) {
-                // padding columns (index >= t_cnt) can only surface when t_cnt < 2
-                if (s.i1 >= t_cnt) s.i1 = -1;
-                if (s.i2 >= t_cnt) s.i2 = -1;
-                const int d1 = s.i1 < 0 ? INT_MAX : s.d1 + na;
-                const int d2 = s.i2 < 0 ? INT_MAX : s.d2 + na;
-                out[out_row + row] = make_int4(s.i1, s.i2, d1, d2);
+                if (!FOLD) {
+                    // padding columns (index >= t_cnt) can only surface when t_cnt < 2
+                    if (s.i1 >= t_cnt) s.i1 = -1;
+                    if (s.i2 >= t_cnt) s.i2 = -1;
+                    const int d1 = s.i1 < 0 ? INT_MAX : s.d1 + na;
+                    const int d2 = s.i2 < 0 ? INT_MAX : s.d2 + na;
+                    out[out_row + row] = make_int4(s.i1, s.i2, d1, d2);
+                } else if (MODE == kFoldFastOnly) {
+                    out[out_row + row] = make_int4(sk.k1, sk.k2, na, 0);   // keeps the probe's work live
+                } else {
+                    const int d1 = sk.i1 < 0 ? INT_MAX : na - sk.k1;
+                    const int d2 = sk.i2 < 0 ? INT_MAX : na - sk.k2;
+                    out[out_row + row] = make_int4(sk.i1, sk.i2, d1, d2);
+                }
             }
         }
     }
@@ -291,14 +476,16 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const WorkItem* __restrict
 // ---------------------------------------------------------------------------
 // Debug: one 128x128 tile of raw dot products through the same TMA/UMMA path.
 __global__ void __launch_bounds__(128, 1)
-debug_dot_kernel(const __grid_constant__ CUtensorMap tmap, int q_row, int t_row,
-                 int32_t* __restrict__ out) {
+debug_dot_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
+                 int q_row, int t_row, int x_row, int x_chunk, int32_t* __restrict__ out) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     uint8_t* sa = base;
     uint8_t* sb = base + kTileBytes;
-    uint64_t* bar_ld = reinterpret_cast<uint64_t*>(base + 2 * kTileBytes);
+    uint8_t* sx = base + 2 * kTileBytes;    // bias tile (fold step B operand)
+    uint8_t* sax = base + 3 * kTileBytes;   // constant fold-step A operand
+    uint64_t* bar_ld = reinterpret_cast<uint64_t*>(base + 4 * kTileBytes);
     uint64_t* bar_mma = bar_ld + 1;
     uint32_t* slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -316,9 +503,14 @@ debug_dot_kernel(const __grid_constant__ CUtensorMap tmap, int q_row, int t_row,
     tc_fence_after();
     const uint32_t tmem_base = *slot;
     if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(bar_ld, 2 * kTileBytes);
+        const bool fold = x_row >= 0;
+        mbar_arrive_expect_tx(bar_ld, (fold ? 4 : 2) * kTileBytes);
         tma_load_2d(sa, &tmap, bar_ld, 0, q_row);
         tma_load_2d(sb, &tmap, bar_ld, 0, t_row);
+        if (fold) {
+            tma_load_2d(sx, &tmap_x, bar_ld, 0, x_row);
+            tma_load_2d(sax, &tmap_x, bar_ld, 0, 0);
+        }
         mbar_wait(bar_ld, 0);
         tc_fence_after();
         const uint64_t ad = make_kmajor_sw128_desc(smem_u32(sa));
@@ -326,6 +518,10 @@ debug_dot_kernel(const __grid_constant__ CUtensorMap tmap, int q_row, int t_row,
         for (int k = 0; k < kKSteps; ++k)
             mma_i8_ss(tmem_base, ad + uint64_t(k) * (kUmmaK >> 4), bd + uint64_t(k) * (kUmmaK >> 4),
                       kIdesc, k > 0);
+        if (fold)
+            mma_i8_ss(tmem_base, make_kmajor_sw128_desc(smem_u32(sax)),
+                      make_kmajor_sw128_desc(smem_u32(sx)) + uint64_t(x_chunk) * (kUmmaK >> 4),
+                      kIdesc, 1);
         mma_commit(bar_mma);
     }
     __syncwarp();
@@ -350,8 +546,7 @@ debug_dot_kernel(const __grid_constant__ CUtensorMap tmap, int q_row, int t_row,
 // ---------------------------------------------------------------------------
 // Tensor-pipe peak probe: MMA-only loop (operands are whatever is in shared
 // memory; the integer pipe's rate does not depend on the data).
-constexpr int kProbeN = 256;
-__global__ void __launch_bounds__(128, 1) mma_probe_kernel(int iters) {
+__global__ void __launch_bounds__(128, 1) mma_probe_kernel(int iters, int probe_n) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -378,9 +573,9 @@ __global__ void __launch_bounds__(128, 1) mma_probe_kernel(int iters) {
     if (threadIdx.x == 0) {
         const uint64_t ad = make_kmajor_sw128_desc(smem_u32(sa));
         const uint64_t bd = make_kmajor_sw128_desc(smem_u32(sb));
-        constexpr uint32_t idesc = make_idesc_u8(128, kProbeN);
+        const uint32_t idesc = make_idesc_u8(128, probe_n);
         for (int it = 0; it < iters; ++it) {
-            const uint32_t d = tmem_base + (it & 1) * kProbeN;
+            const uint32_t d = tmem_base + (it & 1) * probe_n;
 #pragma unroll
             for (int k = 0; k < kKSteps; ++k)
                 mma_i8_ss(d, ad + uint64_t(k) * (kUmmaK >> 4), bd + uint64_t(k) * (kUmmaK >> 4), idesc,
@@ -426,11 +621,63 @@ __global__ void pad_norms_kernel(const int32_t* __restrict__ norms,
         norms_pad[p0 + c] = c < n ? norms[r0 + c] : kPadNorm;
 }
 
+// Fold-step operands (see the header comment): row 0..127 of the bias array is
+// the constant A operand (1, 255 x 31 in the first 32 bytes of each 128-byte
+// row); from row x_off[img] on, 128-byte row (g * 128 + r) holds in its 32-byte
+// chunk j the u8 digits of C - floor(||b||^2 / 2) for train row g * 512 + j * 128 + r
+// of image img, i.e. one 128 x 128-byte SWIZZLE_128B TMA box serves 4 train tiles.
+__global__ void bias_kernel(const int32_t* __restrict__ norms, const long long* __restrict__ img_off,
+                            const long long* __restrict__ x_off, int n_images,
+                            uint8_t* __restrict__ bias, int32_t* __restrict__ flags) {
+    const int img = blockIdx.y;
+    if (img >= n_images) return;
+    const long long r0 = img_off[img], n = img_off[img + 1] - r0;
+    const long long x0 = x_off[img], nx = (x_off[img + 1] - x0) * kXGroup;   // (row, chunk) slots
+    for (long long sidx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; sidx < nx;
+         sidx += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long xr = sidx / kXGroup;          // bias row within the image
+        const int j = static_cast<int>(sidx % kXGroup);
+        const long long trow = (xr / kTileM) * (kXGroup * kTileM) + j * kTileM + (xr % kTileM);
+        int h = 0;
+        if (trow < n) {
+            h = norms[r0 + trow] >> 1;
+            if (h > kFoldC) {
+                h = kFoldC;
+                atomicOr(flags, 1);
+            }
+        }
+        const int u = kFoldC - h;
+        int q = u / 255;
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = 0;
+        w[0] = static_cast<uint32_t>(u % 255);          // digit 0, weight 1
+#pragma unroll
+        for (int k = 1; k < 32; ++k) {                  // digits 1..31, weight 255
+            const int take = q < 255 ? q : 255;
+            w[k >> 2] |= static_cast<uint32_t>(take) << (8 * (k & 3));
+            q -= take;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(bias + (x0 + xr) * kRowBytes + j * kUmmaK);
+        dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+        dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
+}
+
+__global__ void bias_const_kernel(uint8_t* __restrict__ bias) {
+    // 128 rows x 128 bytes; bytes 0..31 = (1, 255 x 31), the rest 0
+    for (int i = threadIdx.x; i < kTileM * kRowBytes; i += blockDim.x) {
+        const int c = i % kRowBytes;
+        bias[i] = c == 0 ? 1 : c < 32 ? 255 : 0;
+    }
+}
+
 __global__ void build_work_kernel(const int32_t* __restrict__ pairs, int n_pairs,
                                   const long long* __restrict__ blk_prefix,
                                   const long long* __restrict__ row_off,
                                   const long long* __restrict__ img_off,
-                                  const long long* __restrict__ pad_off, WorkItem* __restrict__ work) {
+                                  const long long* __restrict__ pad_off,
+                                  const long long* __restrict__ x_off, WorkItem* __restrict__ work) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pairs) return;
     const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
@@ -445,7 +692,7 @@ __global__ void build_work_kernel(const int32_t* __restrict__ pairs, int n_pairs
         it.t_row = static_cast<int32_t>(t0);
         it.t_cnt = static_cast<int32_t>(nt);
         it.t_pad = static_cast<int32_t>(pad_off[ti]);
-        it.reserved = p;
+        it.x_row = static_cast<int32_t>(x_off[ti]);
         it.out_row = row_off[p] + b * SFM_QBLOCK;
         work[w0 + b] = it;
     }
@@ -454,74 +701,112 @@ __global__ void build_work_kernel(const int32_t* __restrict__ pairs, int n_pairs
 }  // namespace
 
 void launch_norms(const uint8_t* d_desc, int64_t total_rows, const int64_t* d_img_off,
-                  const int64_t* d_pad_off, int32_t n_images, int64_t pad_total, int32_t* d_norms,
-                  int32_t* d_norms_pad, cudaStream_t st, int64_t* launches) {
-    (void)pad_total;
+                  const int64_t* d_pad_off, const int64_t* d_x_off, int32_t n_images,
+                  int32_t* d_norms, int32_t* d_norms_pad, uint8_t* d_bias, int32_t* d_flags,
+                  cudaStream_t st, int64_t* launches) {
     if (total_rows > 0) {
         const int threads = 256;
         const long long blocks = (total_rows * 32 + threads - 1) / threads;
         norms_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(d_desc, total_rows, d_norms);
         ++*launches;
     }
-    if (n_images > 0) {
-        // images are processed in slabs of 65535 (grid.y limit)
-        for (int i0 = 0; i0 < n_images; i0 += 65535) {
-            const int cnt = n_images - i0 < 65535 ? n_images - i0 : 65535;
-            dim3 grid(8, cnt);
-            pad_norms_kernel<<<grid, 256, 0, st>>>(d_norms, reinterpret_cast<const long long*>(d_img_off) + i0,
-                                                   reinterpret_cast<const long long*>(d_pad_off) + i0, cnt,
-                                                   d_norms_pad);
-            ++*launches;
-        }
+    cudaMemsetAsync(d_flags, 0, sizeof(int32_t), st);
+    bias_const_kernel<<<1, 256, 0, st>>>(d_bias);
+    ++*launches;
+    // images are processed in slabs of 65535 (grid.y limit)
+    for (int i0 = 0; i0 < n_images; i0 += 65535) {
+        const int cnt = n_images - i0 < 65535 ? n_images - i0 : 65535;
+        dim3 grid(8, cnt);
+        pad_norms_kernel<<<grid, 256, 0, st>>>(d_norms, reinterpret_cast<const long long*>(d_img_off) + i0,
+                                               reinterpret_cast<const long long*>(d_pad_off) + i0, cnt,
+                                               d_norms_pad);
+        bias_kernel<<<grid, 256, 0, st>>>(d_norms, reinterpret_cast<const long long*>(d_img_off) + i0,
+                                          reinterpret_cast<const long long*>(d_x_off) + i0, cnt, d_bias,
+                                          d_flags);
+        *launches += 2;
     }
 }
 
 void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_blk_prefix,
                        const int64_t* d_row_off, const int64_t* d_img_off, const int64_t* d_pad_off,
-                       WorkItem* d_work, cudaStream_t st, int64_t* launches) {
+                       const int64_t* d_x_off, WorkItem* d_work, cudaStream_t st, int64_t* launches) {
     if (n_pairs <= 0) return;
     build_work_kernel<<<(n_pairs + 127) / 128, 128, 0, st>>>(
         d_pairs, n_pairs, reinterpret_cast<const long long*>(d_blk_prefix),
         reinterpret_cast<const long long*>(d_row_off), reinterpret_cast<const long long*>(d_img_off),
-        reinterpret_cast<const long long*>(d_pad_off), d_work);
+        reinterpret_cast<const long long*>(d_pad_off), reinterpret_cast<const long long*>(d_x_off), d_work);
     ++*launches;
 }
 
-int launch_knn2(const CUtensorMap& tmap, const WorkItem* d_work, int64_t n_work,
-                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_knn, int num_sms,
-                cudaStream_t st, int64_t* launches) {
-    if (n_work <= 0) return 0;
+namespace {
+template <int MODE>
+cudaError_t launch_knn2_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work,
+                                int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
+                                const int32_t* d_flags, int force, const KnnTuning& tn, int32_t* d_knn,
+                                unsigned grid, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(knn2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(knn2_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(kSmemBytes));
-        if (e != cudaSuccess) return static_cast<int>(e);
+        if (e != cudaSuccess) return e;
         configured = true;
     }
+    knn2_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad,
+                                                          d_flags, force, tn.wait_ns, tn.epi_wait_ns, tn.probe_flags,
+                                                          reinterpret_cast<int4*>(d_knn));
+    return cudaGetLastError();
+}
+}  // namespace
+
+// mode 0: automatic (fold variant unless the norm flag is raised, then generic);
+// 1: generic only; 2: fold only (caller guarantees the norms fit);
+// 3: fold fast path only, 4: fold without epilogue (timing probes, output is not a kNN).
+int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work, int64_t n_work,
+                const int32_t* d_norms, const int32_t* d_norms_pad, const int32_t* d_flags, int mode,
+                const KnnTuning& tn, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches) {
+    if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
-    knn2_kernel<<<grid, kThreads, kSmemBytes, st>>>(tmap, d_work, n_work, d_norms, d_norms_pad,
-                                                    reinterpret_cast<int4*>(d_knn));
-    ++*launches;
-    return static_cast<int>(cudaGetLastError());
+    cudaError_t e = cudaSuccess;
+    if (mode == 0 || mode == 2) {
+        e = launch_knn2_variant<kFold>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags, mode == 2,
+                                       tn, d_knn, grid, st);
+        ++*launches;
+    }
+    if (e == cudaSuccess && (mode == 0 || mode == 1)) {
+        e = launch_knn2_variant<kGeneric>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags,
+                                          mode == 1, tn, d_knn, grid, st);
+        ++*launches;
+    }
+    if (e == cudaSuccess && mode == 3) {
+        e = launch_knn2_variant<kFoldFastOnly>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags, 1,
+                                               tn, d_knn, grid, st);
+        ++*launches;
+    }
+    if (e == cudaSuccess && mode == 4) {
+        e = launch_knn2_variant<kFoldNoEpilogue>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags,
+                                                 1, tn, d_knn, grid, st);
+        ++*launches;
+    }
+    return static_cast<int>(e);
 }
 
-int launch_debug_dot(const CUtensorMap& tmap, int32_t q_row, int32_t t_row, int32_t* d_out,
-                     cudaStream_t st, int64_t* launches) {
-    const size_t smem = 2 * kTileBytes + 64 + 1024;
+int launch_debug_dot(const CUtensorMap& tmap, const CUtensorMap& tmap_x, int32_t q_row, int32_t t_row,
+                     int32_t x_row, int32_t x_chunk, int32_t* d_out, cudaStream_t st, int64_t* launches) {
+    const size_t smem = 4 * kTileBytes + 64 + 1024;
     cudaError_t e = cudaFuncSetAttribute(debug_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return static_cast<int>(e);
-    debug_dot_kernel<<<1, 128, smem, st>>>(tmap, q_row, t_row, d_out);
+    debug_dot_kernel<<<1, 128, smem, st>>>(tmap, tmap_x, q_row, t_row, x_row, x_chunk, d_out);
     ++*launches;
     return static_cast<int>(cudaGetLastError());
 }
 
-int launch_mma_probe(int32_t iters, int num_sms, cudaStream_t st, int64_t* launches) {
+int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t st, int64_t* launches) {
     const size_t smem = 3 * kTileBytes + 64 + 1024;
     cudaError_t e = cudaFuncSetAttribute(mma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return static_cast<int>(e);
-    mma_probe_kernel<<<num_sms, 128, smem, st>>>(iters);
+    mma_probe_kernel<<<num_sms, 128, smem, st>>>(iters, probe_n);
     ++*launches;
     return static_cast<int>(cudaGetLastError());
 }

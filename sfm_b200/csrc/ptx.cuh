@@ -53,6 +53,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// Same, but each probe may suspend the thread for up to `ns` nanoseconds (the
+// hardware wakes it when the phase completes), so a waiting warp does not eat
+// the issue slots of the warps sharing its scheduler.
+__device__ __forceinline__ void mbar_wait_suspend(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    if (ns == 0) {
+        mbar_wait(bar, parity);
+        return;
+    }
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+            : "memory");
+    } while (!ok);
+}
 
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
@@ -143,11 +162,13 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
     return d;
 }
 
-// Instruction descriptor, kind::i8: D = s32, A = B = unsigned 8-bit, both K-major.
-//   bits [4,6) c_format = 2 (S32); [7,10) a_format = 0 (U8); [10,13) b_format = 0 (U8)
+// Instruction descriptor, kind::i8: D = s32, A and B 8-bit integers, both K-major.
+//   bits [4,6) c_format = 2 (S32); [7,10) a_format; [10,13) b_format (0 = U8, 1 = S8)
 //   bit 15/16 a/b major = 0 (K); [17,23) N >> 3; [24,29) M >> 4
-__host__ __device__ constexpr uint32_t make_idesc_u8(int m, int n) {
-    return (2u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc_i8(int m, int n, uint32_t a_fmt, uint32_t b_fmt) {
+    return (2u << 4) | (a_fmt << 7) | (b_fmt << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
+           (static_cast<uint32_t>(m >> 4) << 24);
 }
+__host__ __device__ constexpr uint32_t make_idesc_u8(int m, int n) { return make_idesc_i8(m, n, 0, 0); }
 
 }  // namespace sfm

@@ -46,6 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
+    "sfm_debug_fold_tile", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -88,6 +89,14 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_launch_count.restype = i64
     lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_dot_tile.argtypes = [vp, i64, i64, vp, vp]
+    lib.sfm_probe_int8_rate.argtypes = [vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
+    lib.sfm_debug_fold_tile.argtypes = [vp, i64, i32, i32, vp, vp]
+    lib.sfm_debug_set_knn_mode.argtypes = [vp, i32]
+    lib.sfm_debug_set_knn_waits.argtypes = [vp, i32, i32]
+    lib.sfm_debug_mma_handshake_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), vp]
+    lib.sfm_debug_set_knn_probe_flags.argtypes = [vp, i32]
+    lib.sfm_debug_tmem_ld_probe.argtypes = [vp, i32, i32, i32, C.POINTER(i64), vp]
+    lib.sfm_debug_fold_flag.argtypes = [vp, C.POINTER(i32), vp]
     for name in EXPORTS:
         getattr(lib, name)
     if lib.sfm_abi_version() != ABI_VERSION:
@@ -312,11 +321,53 @@ class Context:
         self._check(self.lib.sfm_probe_int8_peak(self.h, iters, C.byref(ms), C.byref(ops), self._stream()))
         return ops.value / (ms.value * 1e-3) / 1e12, ms.value   # TOP/s, ms
 
+    def probe_int8_rate(self, tile_n, iters=4096):
+        ms, ops = C.c_float(), C.c_double()
+        self._check(self.lib.sfm_probe_int8_rate(self.h, iters, tile_n, C.byref(ms), C.byref(ops), self._stream()))
+        return ops.value / (ms.value * 1e-3) / 1e12, ms.value
+
     def debug_dot_tile(self, q_row, t_row):
         out = self.empty((128, 128), self.torch.int32)
         self._check(self.lib.sfm_debug_dot_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
                                                 self._stream()))
         return out
+
+
+    def debug_fold_tile(self, q_row, train_image, tile):
+        out = self.empty((128, 128), self.torch.int32)
+        self._check(self.lib.sfm_debug_fold_tile(self.h, q_row, train_image, tile,
+                                                 self._dev(out, self.torch.int32), self._stream()))
+        return out
+
+    def tmem_ld_probe(self, warps, variant, iters=4096):
+        """-> bytes of TMEM read per cycle per SM for the given warp count / load shape."""
+        cyc = C.c_int64(0)
+        self._check(self.lib.sfm_debug_tmem_ld_probe(self.h, warps, variant, iters, C.byref(cyc), self._stream()))
+        per = {0: 4096, 1: 4096, 2: 8192, 3: 4096}[variant]
+        return per * iters * warps / cyc.value, cyc.value
+
+    def set_knn_mode(self, mode: int):
+        """0 auto, 1 generic, 2 folded, 3 folded fast path only (timing probe)."""
+        self._check(self.lib.sfm_debug_set_knn_mode(self.h, mode))
+
+    def set_knn_waits(self, wait_ns: int, epi_wait_ns: int):
+        self._check(self.lib.sfm_debug_set_knn_waits(self.h, wait_ns, epi_wait_ns))
+
+    def mma_handshake_probe(self, k_per_acc, flags, consumers, steps=4096):
+        """-> TOP/s of the issue pattern (2 x k_per_acc 128x128x32 MMAs per step)."""
+        ms = C.c_float()
+        self._check(self.lib.sfm_debug_mma_handshake_probe(self.h, steps, k_per_acc, flags, consumers,
+                                                           C.byref(ms), self._stream()))
+        ops = 2.0 * 128 * 128 * 32 * 2 * k_per_acc * steps * 148
+        return ops / (ms.value * 1e-3) / 1e12
+
+    def set_knn_probe_flags(self, flags: int):
+        self._check(self.lib.sfm_debug_set_knn_probe_flags(self.h, flags))
+
+    def fold_flag(self) -> int:
+        f = C.c_int32(-1)
+        self._check(self.lib.sfm_debug_fold_flag(self.h, C.byref(f), self._stream()))
+        return f.value
 
 
 def metrics_to_numpy(t) -> np.ndarray:

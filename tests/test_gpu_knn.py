@@ -161,3 +161,83 @@ def test_knn_8k_config_sample_vs_oracle_and_properties(ctx):
     for i in range(n):                                         # min over rows == min over columns
         for j in range(i + 1, n):
             assert got[i, j, :, 2].min() == got[j, i, :, 2].min()
+
+
+# ---------------------------------------------------------------- kernel variants
+FOLD_C = 255 * 31 * 255 + 254          # sfm_b200/csrc/knn.cu kFoldC
+def _sift_like(sizes, seed):
+    from sfm_b200 import synth
+    s = synth.make_image_set(len(sizes), list(sizes), seed=seed, tie_frac=0.03)
+    return [s.image(i)[0].numpy() for i in range(len(sizes))]
+
+
+def test_fold_step_accumulators(ctx):
+    """The fifth K-step (u8 constants x u8 digits of C - floor(||b||^2/2)) through TMA + tcgen05:
+    accumulators must equal a.b + C - (||b||^2 >> 1) exactly (bias layout, digit encoding)."""
+    descs = _sift_like([300, 1500, 700], 31)
+    off = register(ctx, descs)
+    assert ctx.fold_flag() == 0
+    for q_img, q0, t_img, tile in [(0, 0, 1, 0), (0, 100, 1, 5), (2, 131, 1, 11), (1, 640, 2, 4), (1, 7, 0, 2)]:
+        got = ctx.debug_fold_tile(int(off[q_img]) + q0, t_img, tile).cpu().numpy()
+        a = descs[q_img][q0:q0 + 128].astype(np.int64)
+        b = descs[t_img][tile * 128:(tile + 1) * 128].astype(np.int64)
+        want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
+        assert np.array_equal(got[:len(a), :len(b)], want)
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_knn_variants_match_oracle(ctx, mode):
+    """Generic (1) and folded (2) kernels, forced, on SIFT-like data with partial tiles and ties."""
+    sizes = [1, 2, 5, 127, 128, 129, 383, 512, 513, 640, 1025, 2000]
+    descs = _sift_like(sizes, 32)
+    register(ctx, descs)
+    ctx.set_knn_mode(mode)
+    try:
+        pairs = [(i, j) for i in range(len(sizes)) for j in range(len(sizes)) if sizes[j] >= 2]
+        got, ro = gpu_knn(ctx, pairs)
+    finally:
+        ctx.set_knn_mode(0)
+    for p, (i, j) in enumerate(pairs):
+        check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+
+
+def test_fold_range_limit_and_fallback(ctx):
+    """||b||^2 = 2 C + 1 = 4,032,059 is the largest norm the fold digits encode; one more and
+    sfm_set_images raises the flag so the generic kernel runs.  Results are exact either way."""
+    rng = np.random.default_rng(33)
+    top = np.zeros(128, np.uint8)
+    top[:62] = 255
+    top[62:66] = (22, 4, 3, 0)                                 # 62*255^2 + 484 + 16 + 9 = 4,032,059
+    assert int((top.astype(np.int64) ** 2).sum()) == 2 * FOLD_C + 1
+    d1 = rng.integers(0, 120, (200, 128)).astype(np.uint8)
+    d1[:, 64:] = 0
+    d2 = rng.integers(0, 140, (300, 128)).astype(np.uint8)
+    d2[17] = top
+    d2[211] = top                                              # duplicate of the extreme row: tie -> lowest index
+    d1[5] = top
+    d1[6] = 0                                                  # zero row: norm 0 -> digits of C itself
+    d2[40] = 0
+    register(ctx, [d1, d2])
+    assert ctx.fold_flag() == 0
+    got, ro = gpu_knn(ctx, [(0, 1), (1, 0)])
+    check_pair(got[ro[0]:ro[1]], d1, d2)
+    check_pair(got[ro[1]:ro[2]], d2, d1)
+    over = top.copy()
+    over[65] = 1                                               # 4,032,060 -> h = C + 1
+    d2[100] = over
+    register(ctx, [d1, d2])
+    assert ctx.fold_flag() == 1
+    got, ro = gpu_knn(ctx, [(0, 1), (1, 0)])
+    check_pair(got[ro[0]:ro[1]], d1, d2)
+    check_pair(got[ro[1]:ro[2]], d2, d1)
+
+
+def test_knn_uniform_random_bytes_use_fold(ctx):
+    """Uniform random bytes (||b||^2 ~ 2.8 M) are inside the fold range; forced fold == oracle."""
+    rng = np.random.default_rng(34)
+    descs = [rng.integers(0, 256, (n, 128)).astype(np.uint8) for n in (300, 700)]
+    register(ctx, descs)
+    assert ctx.fold_flag() == 0
+    got, ro = gpu_knn(ctx, [(0, 1), (1, 0)])
+    check_pair(got[ro[0]:ro[1]], descs[0], descs[1])
+    check_pair(got[ro[1]:ro[2]], descs[1], descs[0])
