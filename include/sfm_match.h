@@ -228,6 +228,10 @@ SFM_API int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags);
 /* Reads (synchronising `stream`) whether the registered set exceeded the fold range. */
 SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);
 
+/* Statistics: query rows the folded kNN kernel recomputed by brute force since the last
+ * sfm_set_images (rows whose candidate tracking met an exact tie; see knn.cu).  Synchronises. */
+SFM_API int sfm_debug_brute_rows(sfm_ctx* ctx, int32_t* h_rows, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -316,7 +316,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
     sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
                            ctx->d_x_off.p, ctx->d_work.p, st, &ctx->launches);
-    int r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_work.p, n_work, ctx->d_norms.p,
+    int r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                              ctx->d_norms_pad.p, ctx->d_flags.p, ctx->knn_mode, ctx->knn_tuning, d_knn, ctx->num_sms, st,
                              &ctx->launches);
     if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
@@ -577,6 +577,16 @@ int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream) {
     if (!ctx->d_flags.p) return ctx->fail("no descriptors registered");
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
     SFM_CUDA(ctx, cudaMemcpyAsync(h_flag, ctx->d_flags.p, sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                  static_cast<cudaStream_t>(stream)));
+    SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int sfm_debug_brute_rows(sfm_ctx* ctx, int32_t* h_rows, void* stream) {
+    if (!ctx || !h_rows) return 1;
+    if (!ctx->d_flags.p) return ctx->fail("no descriptors registered");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_rows, ctx->d_flags.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost,
                                   static_cast<cudaStream_t>(stream)));
     SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
     return 0;

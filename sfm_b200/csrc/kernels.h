@@ -36,8 +36,9 @@ struct KnnTuning {
     uint32_t epi_wait_ns = 200;   // same for the epilogue warps' accumulator-ready wait
     uint32_t probe_flags = 0;     // timing probes: bit 0 no B-tile TMA traffic, bit 1 no MMA issue
 };
-int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work, int64_t n_work,
-                const int32_t* d_norms, const int32_t* d_norms_pad, const int32_t* d_flags, int mode,
+int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,
+                const WorkItem* d_work, int64_t n_work,
+                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_flags, int mode,
                 const KnnTuning& tn, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
 int launch_debug_dot(const CUtensorMap& tmap, const CUtensorMap& tmap_x, int32_t q_row, int32_t t_row,
                      int32_t x_row, int32_t x_chunk, int32_t* d_out, cudaStream_t st, int64_t* launches);

@@ -51,16 +51,18 @@ constexpr int kRowBytes = SFM_DESC_DIM;             // K extent in bytes (u8)
 constexpr int kTileBytes = kTileM * kRowBytes;      // 16 KiB (A tile == B tile)
 constexpr int kABlockBytes = kATiles * kTileBytes;  // 32 KiB
 constexpr int kAStages = 2;
-constexpr int kBStages = 6;
+constexpr int kBStages = 4;
 constexpr int kXStages = 2;                          // bias tiles (one per 4 train tiles)
 constexpr int kXGroup = 4;                           // train tiles per bias tile
 constexpr int kTmemStages = 2;
 constexpr int kTmemColsPerStage = kATiles * kTileN;  // 256
 constexpr int kTmemCols = kTmemStages * kTmemColsPerStage;  // 512 = all of TMEM
-constexpr int kEpiWarps = 8;
-constexpr int kProducerWarp = 8;
-constexpr int kMmaWarp = 9;
-constexpr int kThreads = 10 * 32;
+// epilogue warps: 8 for the generic variant (one thread per query row, 128 columns per tile);
+// 16 for the folded variants (two threads per row, 64 columns each): four warps per scheduler
+// hide the TMEM-load and compare latencies of the short per-chunk dependency chains.
+constexpr int kEpiWarpsMax = 16;
+__host__ __device__ constexpr int epi_warps(int mode) { return mode == 0 ? 8 : 16; }
+__host__ __device__ constexpr int knn_threads(int mode) { return (epi_warps(mode) + 2) * 32; }
 constexpr int kUmmaK = 32;                           // bytes of K per tcgen05.mma kind::i8
 constexpr int kKSteps = kRowBytes / kUmmaK;          // 4
 constexpr uint32_t kIdesc = make_idesc_u8(kTileM, kTileN);
@@ -71,9 +73,11 @@ constexpr int kFoldC = 255 * 31 * 255 + 254;
 
 enum KnnMode { kGeneric = 0, kFold = 1, kFoldFastOnly = 2, kFoldNoEpilogue = 3 };
 
+constexpr size_t kSlotBytes = 2 * 2 * kEpiWarpsMax * 32 * 16;   // 2 parked 8-column units per epilogue thread (32 KiB)
+constexpr size_t kXchgBytes = 2 * SFM_QBLOCK * 16 + kEpiWarpsMax * 32 * 4;   // per-row hand-over between the two column halves + published bounds
 constexpr size_t kSmemData = size_t(kAStages) * kABlockBytes + size_t(kBStages) * kTileBytes +
-                             size_t(kXStages + 1) * kTileBytes;
-constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 2 * kTmemStages + 2 * kXStages + 1;
+                             size_t(kXStages + 1) * kTileBytes + kSlotBytes + kXchgBytes;
+constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 4 * kTmemStages + 2 * kXStages + 1;
 constexpr size_t kSmemBytes = kSmemData + kNumBars * 8 + 16 + 1024;  // + alignment slack
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
@@ -136,11 +140,29 @@ __device__ __forceinline__ void top2_chunk(Top2& s, const uint32_t (&acc)[32], c
 }
 
 // ------------------------------------------------------------------ folded epilogue
-// Running top-2 of the exact key K = 2 a.b - ||b||^2 = 2 (v - C) - p (maximised), p the
-// parity of ||b||^2.  `thr` is the smallest folded accumulator v that can still enter:
-// 2 (v - C) - p > k2 for some p in {0,1}  <=>  v >= (k2 >> 1) + 1 + C.
+// The exact ranking key is K = 2 a.b - ||b||^2 = 2 (v - C) - p (maximised), v the folded
+// accumulator and p the parity of ||b||^2.  Both nearest neighbours have v >= V2, the second
+// largest v of the row (K >= 2 V2 - 1 forces v >= V2).  So per row the kernel only tracks the
+// two 16-column UNITS with the largest maxima (m1 >= m2, earliest unit on equal maxima) and
+// parks their 16 accumulators in shared memory; everything exact -- parity, indices, the
+// lowest-index tie rule -- is done once per work item on those 32 values (resolve_units).
+// The steady-state cost is a max3 tree plus two compares per 32 columns.
+// The two units hold every element with v >= V2 unless a unit that is NOT parked has a
+// maximum equal to m2 (an incoming unit with m == m2, or the old second unit evicted by a new
+// best while m2 == m1).  At that moment the row switches to EXACT mode for the rest of the
+// work item: an element-wise running top-2 of K (exact_unit), entered only when a unit
+// maximum reaches the threshold kept in m2.  Exact mode is rare outside all-ties data
+// (0.65 % of rows on the synthetic 8k set) and is always correct.
+struct Cand {
+    int m1, m2;   // units: largest / second largest unit maximum.   exact: k1 / entry threshold on v
+    int c1, c2;   // units: first column of those units (-1: none).  exact: i1 / i2
+    int s1;       // units: shared-memory slot (0/1) of unit c1.     exact: 2
+    int x;        //                                                  exact: k2
+    int thr;      // entry threshold on a unit maximum: max(m2, what the row's other thread published)
+};
+
 struct Top2K {
-    int k1, k2, i1, i2, thr;
+    int k1, k2, i1, i2;
 };
 
 __device__ __forceinline__ void top2k_insert(Top2K& s, int key, int col) {
@@ -154,47 +176,144 @@ __device__ __forceinline__ void top2k_insert(Top2K& s, int key, int col) {
             s.k2 = key;
             s.i2 = col;
         }
-        s.thr = (s.k2 >> 1) + 1 + kFoldC;
     }
 }
 
-// 32 folded accumulators of one row.  `nbp` points at the padded column norms
-// of column col0 (only read on the exact path, for the parity bit).  MASKED:
-// columns >= t_cnt (last, partial train tile) are forced out.
+// (key, index) order of the tie rule: larger key first, then lower index.
+__device__ __forceinline__ bool key_before(int ka, int ia, int kb, int ib) {
+    return ka > kb || (ka == kb && ia < ib);
+}
+
+constexpr int kUnit = 8;
+constexpr uint32_t kSlotRow = kEpiWarpsMax * 32 * 16;       // bytes between a thread's uint4s
+constexpr uint32_t kSlotStride = (kUnit / 4) * kSlotRow;    // bytes per slot
+
+// Exact top-2 of the (at most) two parked units, visited in ascending column order.
+// slots: shared address of this thread's first uint4; layout [slot][4 x uint4][thread]
+__device__ __forceinline__ Top2K resolve_units(const Cand& s, uint32_t slots,
+                                               const int32_t* __restrict__ nbase, int t_cnt) {
+    Top2K r{INT_MIN, INT_MIN, -1, -1};
+    const bool second_first = s.c2 >= 0 && s.c2 < s.c1;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        const bool take2 = (pass == 0) == second_first;
+        const int c = take2 ? s.c2 : s.c1;
+        if (c < 0) continue;
+        const uint32_t src = slots + (take2 ? (s.s1 ^ 1) : s.s1) * kSlotStride;
+#pragma unroll
+        for (int g = 0; g < kUnit / 4; ++g) {
+            const uint4 q = lds128(src + g * kSlotRow);
+            const int4 nb = __ldg(reinterpret_cast<const int4*>(nbase + c) + g);
+            const int vv[4] = {static_cast<int>(q.x), static_cast<int>(q.y), static_cast<int>(q.z),
+                               static_cast<int>(q.w)};
+            const int pp[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int col = c + 4 * g + e;
+                if (col < t_cnt) top2k_insert(r, 2 * vv[e] - (pp[e] + 2 * kFoldC), col);
+            }
+        }
+    }
+    return r;
+}
+
+struct UnitVals {
+    int v[kUnit];
+};
+
+// Rare path: element-wise exact update of one row with one unit (switching the row to exact
+// mode first if it was still tracking units).  Kept out of line: the hot loop only pays a call
+// in an unlikely branch.
+__device__ __noinline__ Cand exact_unit(Cand s, UnitVals in, int col, uint32_t slots,
+                                        const int32_t* __restrict__ nbase, int t_cnt) {
+    Top2K r;
+    if (s.s1 < 2) {
+        r = resolve_units(s, slots, nbase, t_cnt);
+    } else {
+        r = Top2K{s.m1, s.x, s.c1, s.c2};
+    }
+#pragma unroll
+    for (int g = 0; g < kUnit / 4; ++g) {
+        const int4 nb = __ldg(reinterpret_cast<const int4*>(nbase + col) + g);
+        const int pp[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int c = col + 4 * g + e;
+            if (c < t_cnt) top2k_insert(r, 2 * in.v[4 * g + e] - (pp[e] + 2 * kFoldC), c);
+        }
+    }
+    s.m1 = r.k1;
+    s.x = r.k2;
+    s.c1 = r.i1;
+    s.c2 = r.i2;
+    s.s1 = 2;
+    s.m2 = (r.k2 >> 1) + 1 + kFoldC;   // v can enter iff 2 (v - C) - p > k2 for some parity p
+    return s;
+}
+
+// `pub`: shared address where this thread publishes a bound for the row's other thread (the one
+// scanning the other column half): unit maxima below it cannot matter for the row.  In unit
+// mode that is m2 (two of this thread's units reach it); in exact mode the entry threshold
+// minus one, because an element one below it can still TIE this thread's second key and win
+// on the lower index.  Stale values are harmless: the bound only ever rises within a work item.
+template <bool MASKED>
+__device__ __forceinline__ void unit_event(Cand& s, const int (&v)[32], int u, int m, int col,
+                                           uint32_t slots, uint32_t pub, const int32_t* __restrict__ nbase,
+                                           int t_cnt) {
+    if (m >= s.thr && (!MASKED || m > kNegV)) {
+        const bool new_best = m > s.m1;
+        // a unit with maximum == m2 would stay unparked: the incoming one, or the evicted second
+        const bool tie = m == s.m2 || (new_best && s.m2 == s.m1 && s.c2 >= 0);
+        if (s.s1 < 2 && !tie) {
+            const uint32_t dst = slots + (s.s1 ^ 1) * kSlotStride;
+#pragma unroll
+            for (int g = 0; g < kUnit / 4; ++g)
+                sts128(dst + g * kSlotRow, v[u * kUnit + 4 * g], v[u * kUnit + 4 * g + 1],
+                       v[u * kUnit + 4 * g + 2], v[u * kUnit + 4 * g + 3]);
+            if (new_best) {
+                s.m2 = s.m1;
+                s.c2 = s.c1;
+                s.m1 = m;
+                s.c1 = col;
+                s.s1 ^= 1;
+            } else {
+                s.m2 = m;
+                s.c2 = col;
+            }
+        } else {
+            UnitVals in;
+#pragma unroll
+            for (int e = 0; e < kUnit; ++e) in.v[e] = v[u * kUnit + e];
+            s = exact_unit(s, in, col, slots, nbase, t_cnt);
+        }
+        s.thr = max(s.thr, s.m2);
+        sts32(pub, static_cast<uint32_t>(s.s1 == 2 ? s.m2 - 1 : s.m2));
+    }
+}
+
+// 32 folded accumulators of one row = four units.  MASKED: columns >= t_cnt (last, partial
+// train tile) are forced to kNegV.
 template <bool MASKED, int MODE>
-__device__ __forceinline__ void fold_chunk(Top2K& s, const uint32_t (&acc)[32],
-                                           const int32_t* __restrict__ nbp, int col0, int t_cnt) {
+__device__ __forceinline__ void fold_chunk(Cand& s, const uint32_t (&acc)[32], int col0, int t_cnt,
+                                           uint32_t slots, uint32_t pub, const int32_t* __restrict__ nbase) {
     int v[32];
 #pragma unroll
     for (int e = 0; e < 32; ++e) {
         v[e] = static_cast<int>(acc[e]);
         if (MASKED) v[e] = (col0 + e < t_cnt) ? v[e] : kNegV;
     }
-    int m4[8];
+    int m8[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-        m4[j] = max(__vimax3_s32(v[4 * j], v[4 * j + 1], v[4 * j + 2]), v[4 * j + 3]);
-    const int m = max(__vimax3_s32(__vimax3_s32(m4[0], m4[1], m4[2]), __vimax3_s32(m4[3], m4[4], m4[5]),
-                                   m4[6]),
-                      m4[7]);
+    for (int j = 0; j < 4; ++j)
+        m8[j] = max(__vimax3_s32(__vimax3_s32(v[8 * j], v[8 * j + 1], v[8 * j + 2]),
+                                 __vimax3_s32(v[8 * j + 3], v[8 * j + 4], v[8 * j + 5]), v[8 * j + 6]),
+                    v[8 * j + 7]);
     if (MODE == kFoldFastOnly) {
-        s.k1 = max(s.k1, m);   // timing probe: fast path only (results are not a kNN)
+        s.m1 = max(__vimax3_s32(s.m1, m8[0], m8[1]), max(m8[2], m8[3]));   // timing probe: tree only
         return;
     }
-    if (m >= s.thr) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (m4[j] >= s.thr) {
-                const int4 nb = __ldg(reinterpret_cast<const int4*>(nbp) + j);
-                const int c = col0 + 4 * j;
-                const int p4[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
-#pragma unroll
-                for (int e = 0; e < 4; ++e)
-                    if (!MASKED || c + e < t_cnt)   // masked columns never enter, whatever the state
-                        top2k_insert(s, 2 * v[4 * j + e] - (p4[e] + 2 * kFoldC), c + e);
-            }
-        }
-    }
+    for (int j = 0; j < 4; ++j) unit_event<MASKED>(s, v, j, m8[j], col0 + j * kUnit, slots, pub, nbase, t_cnt);
 }
 
 struct SmemLayout {
@@ -202,6 +321,9 @@ struct SmemLayout {
     uint8_t* b;
     uint8_t* x;    // kXStages bias tiles
     uint8_t* ax;   // constant A operand of the fold step
+    uint4* slots;  // parked candidate units of the folded epilogue
+    uint4* xchg;   // [2][256] per-row results handed from the upper to the lower column half
+    int32_t* pub;  // [512] bound each folded-epilogue thread publishes for its row's other thread
     uint64_t* a_full;
     uint64_t* a_empty;
     uint64_t* b_full;
@@ -219,14 +341,17 @@ struct SmemLayout {
         b = a + size_t(kAStages) * kABlockBytes;
         x = b + size_t(kBStages) * kTileBytes;
         ax = x + size_t(kXStages) * kTileBytes;
+        slots = reinterpret_cast<uint4*>(ax + kTileBytes);
+        xchg = reinterpret_cast<uint4*>(ax + kTileBytes + kSlotBytes);
+        pub = reinterpret_cast<int32_t*>(ax + kTileBytes + kSlotBytes + 2 * SFM_QBLOCK * 16);
         uint64_t* bars = reinterpret_cast<uint64_t*>(base + kSmemData);
         a_full = bars;
         a_empty = a_full + kAStages;
         b_full = a_empty + kAStages;
         b_empty = b_full + kBStages;
         t_full = b_empty + kBStages;
-        t_empty = t_full + kTmemStages;
-        x_full = t_empty + kTmemStages;
+        t_empty = t_full + 2 * kTmemStages;   // [stage][accumulator]
+        x_full = t_empty + 2 * kTmemStages;
         x_empty = x_full + kXStages;
         ax_full = x_empty + kXStages;
         tmem_slot = reinterpret_cast<uint32_t*>(ax_full + 1);
@@ -237,13 +362,20 @@ struct SmemLayout {
 // encode -> only the generic variant may run.  Both variants are launched
 // back to back (no host synchronisation); the one that does not apply exits.
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(knn_threads(MODE), 1)
 knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
-            const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms,
-            const int32_t* __restrict__ norms_pad, const int32_t* __restrict__ flags, int force,
+            const uint8_t* __restrict__ desc, const WorkItem* __restrict__ work, long long n_work,
+            const int32_t* __restrict__ norms,
+            const int32_t* __restrict__ norms_pad, int32_t* __restrict__ flags, int force,
             uint32_t wait_ns, uint32_t epi_wait_ns, uint32_t probe_flags, int4* __restrict__ out) {
     constexpr bool FOLD = MODE != kGeneric;
-    if (!force && ((__ldg(flags) != 0) == FOLD)) return;
+    constexpr int kEpiWarps = epi_warps(MODE);
+    constexpr int kProducerWarp = kEpiWarps;
+    constexpr int kMmaWarp = kEpiWarps + 1;
+    constexpr int kHalves = kEpiWarps / 8;             // threads (column ranges) per query row
+    constexpr int kColsPerThread = kTileN / kHalves;   // columns of each train tile per thread
+    constexpr int kChunks = kColsPerThread / 32;
+    if (!force && ((*static_cast<volatile const int32_t*>(flags) != 0) == FOLD)) return;
 
     extern __shared__ uint8_t smem_raw[];
     SmemLayout sm(smem_raw);
@@ -261,9 +393,9 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
             mbar_init(&sm.b_full[i], 1);
             mbar_init(&sm.b_empty[i], 1);
         }
-        for (int i = 0; i < kTmemStages; ++i) {
+        for (int i = 0; i < 2 * kTmemStages; ++i) {   // [stage][accumulator]
             mbar_init(&sm.t_full[i], 1);
-            mbar_init(&sm.t_empty[i], kEpiWarps);
+            mbar_init(&sm.t_empty[i], kEpiWarps / kATiles);
         }
         for (int i = 0; i < kXStages; ++i) {
             mbar_init(&sm.x_full[i], 1);
@@ -351,19 +483,21 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
                     mbar_wait_suspend(&sm.x_full[xp.stage], xp.phase, wait_ns);
                     xdesc0 = make_kmajor_sw128_desc(smem_u32(sm.x + size_t(xp.stage) * kTileBytes));
                 }
-                mbar_wait_suspend(&sm.t_empty[tp.stage], tp.phase ^ 1, wait_ns);
                 mbar_wait_suspend(&sm.b_full[bp.stage], bp.phase, wait_ns);
-                tc_fence_after();
                 const uint64_t bdesc0 = make_kmajor_sw128_desc(smem_u32(sm.b + size_t(bp.stage) * kTileBytes));
                 const uint64_t xdesc = xdesc0 + uint64_t(t % kXGroup) * (kUmmaK >> 4);
                 const uint32_t d0 = tmem_base + tp.stage * kTmemColsPerStage;
                 const bool x_done = FOLD && ((t % kXGroup) == kXGroup - 1 || t == n_tiles - 1);
-                if (elect_one()) {
-                    if (!(probe_flags & 2u)) {   // (probe bit 1: no MMA issue)
 #pragma unroll
-                        for (int a = 0; a < kATiles; ++a) {
-                            const uint32_t d = d0 + a * kTileN;
-                            const uint64_t adesc = adesc0 + uint64_t(a) * (kTileBytes >> 4);
+                for (int a = 0; a < kATiles; ++a) {
+                    // each 128-row accumulator is handed over on its own barrier pair, so the
+                    // epilogue of accumulator 0 overlaps the MMAs of accumulator 1
+                    mbar_wait_suspend(&sm.t_empty[tp.stage * kATiles + a], tp.phase ^ 1, wait_ns);
+                    tc_fence_after();
+                    const uint32_t d = d0 + a * kTileN;
+                    const uint64_t adesc = adesc0 + uint64_t(a) * (kTileBytes >> 4);
+                    if (elect_one()) {
+                        if (!(probe_flags & 2u)) {   // (probe bit 1: no MMA issue)
 #pragma unroll
                             for (int k = 0; k < kKSteps; ++k)
                                 mma_i8_ss(d, adesc + uint64_t(k) * (kUmmaK >> 4),
@@ -371,10 +505,13 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
                             if (FOLD)   // + (1, 255 x 31) . digits(C - floor(||b||^2 / 2))
                                 mma_i8_ss(d, axdesc, xdesc, kIdesc, 1);
                         }
+                        mma_commit(&sm.t_full[tp.stage * kATiles + a]);   // accumulator ready for the epilogue
+                        if (a == kATiles - 1) {
+                            mma_commit(&sm.b_empty[bp.stage]);   // B slot reusable once the MMAs retire
+                            if (x_done) mma_commit(&sm.x_empty[xp.stage]);
+                        }
                     }
-                    mma_commit(&sm.b_empty[bp.stage]);   // B slot reusable once the MMAs retire
-                    mma_commit(&sm.t_full[tp.stage]);    // accumulators ready for the epilogue
-                    if (x_done) mma_commit(&sm.x_empty[xp.stage]);
+                    __syncwarp();
                 }
                 __syncwarp();
                 if (x_done) xp.advance();
@@ -387,12 +524,23 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
         }
     } else {
         // ------------------------------------------------ epilogue warps
-        const int quad = warp & 3;   // TMEM lane quadrant this warp may read
-        const int acc = warp >> 2;   // which 128-row accumulator of the stage
+        const int quad = warp & 3;          // TMEM lane quadrant this warp may read
+        const int acc = (warp >> 2) & 1;    // which 128-row accumulator of the stage
+        const int half = warp >> 3;         // which column range of every tile (folded variants: 0/1)
         const int row = acc * kTileM + quad * 32 + lane;
-        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kTileN;
+        const int colbase = half * kColsPerThread;
+        const uint32_t lane_addr =
+            tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kTileN + colbase;
+        const uint32_t my_slots = smem_u32(sm.slots) + threadIdx.x * 16;
+        const uint32_t my_pub = smem_u32(sm.pub) + threadIdx.x * 4;
+        const uint32_t other_pub = smem_u32(sm.pub) + (threadIdx.x ^ (8 * 32)) * 4;
+        if (FOLD && kHalves == 2) {
+            sts32(my_pub, static_cast<uint32_t>(INT_MIN));
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp & 7)) : "memory");
+        }
         Pipe tp(kTmemStages);
-        for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
+        int item = 0;
+        for (long long w = blockIdx.x; w < n_work; w += gridDim.x, ++item) {
             const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
             const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
             const int q_row = w0.x, q_cnt = w0.y, t_cnt = w0.w, t_pad = w1.x;
@@ -403,24 +551,27 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
             const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
             const int32_t* nbase = norms_pad + t_pad;
             Top2 s{INT_MAX, INT_MAX, -1, -1};
-            Top2K sk{INT_MIN, INT_MIN, -1, -1, (INT_MIN >> 1) + 1 + kFoldC};
+            Cand sk{INT_MIN, INT_MIN, -1, -1, 0, 0, INT_MIN};
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait_suspend(&sm.t_full[tp.stage], tp.phase, epi_wait_ns);
+                uint64_t* full = &sm.t_full[tp.stage * kATiles + acc];
+                uint64_t* empty = &sm.t_empty[tp.stage * kATiles + acc];
+                mbar_wait_suspend(full, tp.phase, epi_wait_ns);
                 tc_fence_after();
-                const uint32_t taddr = lane_addr + tp.stage * kTmemColsPerStage;
                 if (MODE == kFoldNoEpilogue) {   // timing probe: TMA + MMA pipeline alone
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&sm.t_empty[tp.stage]);
+                    if (lane == 0) mbar_arrive(empty);
                     tp.advance();
                     continue;
                 }
+                const uint32_t taddr = lane_addr + tp.stage * kTmemColsPerStage;
                 const bool partial = FOLD && (t + 1) * kTileN > t_cnt;
+                if (FOLD && kHalves == 2) sk.thr = max(sk.thr, static_cast<int>(lds32(other_pub)));
                 uint32_t v[2][32];
                 tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-                for (int c = 0; c < kTileN / 32; ++c) {
-                    const int col0 = t * kTileN + c * 32;
+                for (int c = 0; c < kChunks; ++c) {
+                    const int col0 = t * kTileN + colbase + c * 32;
                     int4 nb[8];
                     if (!FOLD) {
 #pragma unroll
@@ -428,38 +579,79 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
                             nb[j] = __ldg(reinterpret_cast<const int4*>(nbase) + col0 / 4 + j);
                     }
                     tmem_ld_wait();
-                    if (c + 1 < kTileN / 32) {
+                    if (c + 1 < kChunks) {
                         tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
                     } else {
-                        // every column of this stage is in registers: hand it back
+                        // every column of this thread is in registers: hand the accumulator back
                         tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&sm.t_empty[tp.stage]);
+                        if (lane == 0) mbar_arrive(empty);
                     }
                     if (!FOLD) {
                         top2_chunk(s, v[c & 1], nb, col0);
                     } else if (partial) {
-                        fold_chunk<true, MODE>(sk, v[c & 1], nbase + col0, col0, t_cnt);
+                        fold_chunk<true, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
                     } else {
-                        fold_chunk<false, MODE>(sk, v[c & 1], nbase + col0, col0, t_cnt);
+                        fold_chunk<false, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
                     }
                 }
                 tp.advance();
             }
-            if (valid) {
-                if (!FOLD) {
+            if (!FOLD) {
+                if (valid) {
                     // padding columns (index >= t_cnt) can only surface when t_cnt < 2
                     if (s.i1 >= t_cnt) s.i1 = -1;
                     if (s.i2 >= t_cnt) s.i2 = -1;
                     const int d1 = s.i1 < 0 ? INT_MAX : s.d1 + na;
                     const int d2 = s.i2 < 0 ? INT_MAX : s.d2 + na;
                     out[out_row + row] = make_int4(s.i1, s.i2, d1, d2);
-                } else if (MODE == kFoldFastOnly) {
-                    out[out_row + row] = make_int4(sk.k1, sk.k2, na, 0);   // keeps the probe's work live
+                }
+            } else if (MODE != kFold) {
+                if (valid && half == 0) out[out_row + row] = make_int4(sk.m1, sk.m2, na, 0);   // keeps the probe live
+            } else {
+                Top2K r;
+                if (sk.s1 == 2) {
+                    r = Top2K{sk.m1, sk.x, sk.c1, sk.c2};
                 } else {
-                    const int d1 = sk.i1 < 0 ? INT_MAX : na - sk.k1;
-                    const int d2 = sk.i2 < 0 ? INT_MAX : na - sk.k2;
-                    out[out_row + row] = make_int4(sk.i1, sk.i2, d1, d2);
+                    r = resolve_units(sk, my_slots, nbase, t_cnt);
+                }
+                const unsigned ex = __ballot_sync(0xffffffffu, valid && sk.s1 == 2);
+                if (ex && lane == 0) atomicAdd(flags + 1, __popc(ex));   // statistics: rows in exact mode
+                // the thread of the upper column half hands its top-2 to the lower half's thread,
+                // which merges under the (key, lowest index) order and writes the row
+                const uint32_t xaddr = smem_u32(sm.xchg) + ((item & 1) * SFM_QBLOCK + row) * 16;
+                if (half == 1) sts128(xaddr, r.k1, r.k2, r.i1, r.i2);
+                sts32(my_pub, static_cast<uint32_t>(INT_MIN));   // next work item starts unbounded
+                asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp & 7)) : "memory");
+                if (half == 0) {
+                    const uint4 o = lds128(xaddr);
+                    Top2K b{static_cast<int>(o.x), static_cast<int>(o.y), static_cast<int>(o.z),
+                            static_cast<int>(o.w)};
+                    if (b.i1 < 0) b.i1 = INT_MAX;   // empty entries sort last
+                    if (b.i2 < 0) b.i2 = INT_MAX;
+                    if (r.i1 < 0) r.i1 = INT_MAX;
+                    if (r.i2 < 0) r.i2 = INT_MAX;
+                    Top2K mrg;
+                    if (key_before(r.k1, r.i1, b.k1, b.i1)) {
+                        mrg.k1 = r.k1;
+                        mrg.i1 = r.i1;
+                        const bool mine = key_before(r.k2, r.i2, b.k1, b.i1);
+                        mrg.k2 = mine ? r.k2 : b.k1;
+                        mrg.i2 = mine ? r.i2 : b.i1;
+                    } else {
+                        mrg.k1 = b.k1;
+                        mrg.i1 = b.i1;
+                        const bool theirs = key_before(b.k2, b.i2, r.k1, r.i1);
+                        mrg.k2 = theirs ? b.k2 : r.k1;
+                        mrg.i2 = theirs ? b.i2 : r.i1;
+                    }
+                    if (valid) {
+                        const int i1 = mrg.i1 == INT_MAX ? -1 : mrg.i1;
+                        const int i2 = mrg.i2 == INT_MAX ? -1 : mrg.i2;
+                        const int d1 = i1 < 0 ? INT_MAX : na - mrg.k1;
+                        const int d2 = i2 < 0 ? INT_MAX : na - mrg.k2;
+                        out[out_row + row] = make_int4(i1, i2, d1, d2);
+                    }
                 }
             }
         }
@@ -710,7 +902,7 @@ void launch_norms(const uint8_t* d_desc, int64_t total_rows, const int64_t* d_im
         norms_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(d_desc, total_rows, d_norms);
         ++*launches;
     }
-    cudaMemsetAsync(d_flags, 0, sizeof(int32_t), st);
+    cudaMemsetAsync(d_flags, 0, 4 * sizeof(int32_t), st);
     bias_const_kernel<<<1, 256, 0, st>>>(d_bias);
     ++*launches;
     // images are processed in slabs of 65535 (grid.y limit)
@@ -740,9 +932,10 @@ void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d
 
 namespace {
 template <int MODE>
-cudaError_t launch_knn2_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work,
+cudaError_t launch_knn2_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,
+                                const WorkItem* d_work,
                                 int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
-                                const int32_t* d_flags, int force, const KnnTuning& tn, int32_t* d_knn,
+                                int32_t* d_flags, int force, const KnnTuning& tn, int32_t* d_knn,
                                 unsigned grid, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
@@ -751,7 +944,7 @@ cudaError_t launch_knn2_variant(const CUtensorMap& tmap, const CUtensorMap& tmap
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    knn2_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad,
+    knn2_kernel<MODE><<<grid, knn_threads(MODE), kSmemBytes, st>>>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad,
                                                           d_flags, force, tn.wait_ns, tn.epi_wait_ns, tn.probe_flags,
                                                           reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
@@ -761,29 +954,30 @@ cudaError_t launch_knn2_variant(const CUtensorMap& tmap, const CUtensorMap& tmap
 // mode 0: automatic (fold variant unless the norm flag is raised, then generic);
 // 1: generic only; 2: fold only (caller guarantees the norms fit);
 // 3: fold fast path only, 4: fold without epilogue (timing probes, output is not a kNN).
-int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const WorkItem* d_work, int64_t n_work,
-                const int32_t* d_norms, const int32_t* d_norms_pad, const int32_t* d_flags, int mode,
+int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,
+                const WorkItem* d_work, int64_t n_work,
+                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_flags, int mode,
                 const KnnTuning& tn, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches) {
     if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
     cudaError_t e = cudaSuccess;
     if (mode == 0 || mode == 2) {
-        e = launch_knn2_variant<kFold>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags, mode == 2,
+        e = launch_knn2_variant<kFold>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, mode == 2,
                                        tn, d_knn, grid, st);
         ++*launches;
     }
     if (e == cudaSuccess && (mode == 0 || mode == 1)) {
-        e = launch_knn2_variant<kGeneric>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags,
+        e = launch_knn2_variant<kGeneric>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags,
                                           mode == 1, tn, d_knn, grid, st);
         ++*launches;
     }
     if (e == cudaSuccess && mode == 3) {
-        e = launch_knn2_variant<kFoldFastOnly>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags, 1,
+        e = launch_knn2_variant<kFoldFastOnly>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1,
                                                tn, d_knn, grid, st);
         ++*launches;
     }
     if (e == cudaSuccess && mode == 4) {
-        e = launch_knn2_variant<kFoldNoEpilogue>(tmap, tmap_x, d_work, n_work, d_norms, d_norms_pad, d_flags,
+        e = launch_knn2_variant<kFoldNoEpilogue>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags,
                                                  1, tn, d_knn, grid, st);
         ++*launches;
     }

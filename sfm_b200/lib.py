@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_debug_fold_tile", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_set_knn_probe_flags",
+    "sfm_debug_fold_tile", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -97,6 +97,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_debug_set_knn_probe_flags.argtypes = [vp, i32]
     lib.sfm_debug_tmem_ld_probe.argtypes = [vp, i32, i32, i32, C.POINTER(i64), vp]
     lib.sfm_debug_fold_flag.argtypes = [vp, C.POINTER(i32), vp]
+    lib.sfm_debug_brute_rows.argtypes = [vp, C.POINTER(i32), vp]
     for name in EXPORTS:
         getattr(lib, name)
     if lib.sfm_abi_version() != ABI_VERSION:
@@ -360,6 +361,11 @@ class Context:
                                                            C.byref(ms), self._stream()))
         ops = 2.0 * 128 * 128 * 32 * 2 * k_per_acc * steps * 148
         return ops / (ms.value * 1e-3) / 1e12
+
+    def brute_rows(self) -> int:
+        f = C.c_int32(-1)
+        self._check(self.lib.sfm_debug_brute_rows(self.h, C.byref(f), self._stream()))
+        return f.value
 
     def set_knn_probe_flags(self, flags: int):
         self._check(self.lib.sfm_debug_set_knn_probe_flags(self.h, flags))
