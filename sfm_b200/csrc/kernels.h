@@ -32,8 +32,8 @@ void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d
                        const int64_t* d_row_off, const int64_t* d_img_off, const int64_t* d_pad_off,
                        const int64_t* d_x_off, WorkItem* d_work, cudaStream_t st, int64_t* launches);
 struct KnnTuning {
-    uint32_t wait_ns = 2000;      // mbarrier suspend hint of the producer / MMA warps (0 = spin)
-    uint32_t epi_wait_ns = 200;   // same for the epilogue warps' accumulator-ready wait
+    uint32_t wait_ns = 0;         // mbarrier suspend hint of the producer / MMA warps (0 = spin; measured best)
+    uint32_t epi_wait_ns = 0;     // same for the epilogue warps' accumulator-ready wait
     uint32_t probe_flags = 0;     // timing probes: bit 0 no B-tile TMA traffic, bit 1 no MMA issue
 };
 int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,

@@ -257,7 +257,7 @@ __device__ __noinline__ Cand exact_unit(Cand s, UnitVals in, int col, uint32_t s
 // minus one, because an element one below it can still TIE this thread's second key and win
 // on the lower index.  Stale values are harmless: the bound only ever rises within a work item.
 template <bool MASKED>
-__device__ __forceinline__ void unit_event(Cand& s, const int (&v)[32], int u, int m, int col,
+__device__ __forceinline__ void unit_event(Cand& s, const int (&v)[16], int u, int m, int col,
                                            uint32_t slots, uint32_t pub, const int32_t* __restrict__ nbase,
                                            int t_cnt) {
     if (m >= s.thr && (!MASKED || m > kNegV)) {
@@ -291,29 +291,29 @@ __device__ __forceinline__ void unit_event(Cand& s, const int (&v)[32], int u, i
     }
 }
 
-// 32 folded accumulators of one row = four units.  MASKED: columns >= t_cnt (last, partial
+// 16 folded accumulators of one row = two units.  MASKED: columns >= t_cnt (last, partial
 // train tile) are forced to kNegV.
 template <bool MASKED, int MODE>
-__device__ __forceinline__ void fold_chunk(Cand& s, const uint32_t (&acc)[32], int col0, int t_cnt,
+__device__ __forceinline__ void fold_chunk(Cand& s, const uint32_t (&acc)[16], int col0, int t_cnt,
                                            uint32_t slots, uint32_t pub, const int32_t* __restrict__ nbase) {
-    int v[32];
+    int v[16];
 #pragma unroll
-    for (int e = 0; e < 32; ++e) {
+    for (int e = 0; e < 16; ++e) {
         v[e] = static_cast<int>(acc[e]);
         if (MASKED) v[e] = (col0 + e < t_cnt) ? v[e] : kNegV;
     }
-    int m8[4];
+    int m8[2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 2; ++j)
         m8[j] = max(__vimax3_s32(__vimax3_s32(v[8 * j], v[8 * j + 1], v[8 * j + 2]),
                                  __vimax3_s32(v[8 * j + 3], v[8 * j + 4], v[8 * j + 5]), v[8 * j + 6]),
                     v[8 * j + 7]);
     if (MODE == kFoldFastOnly) {
-        s.m1 = max(__vimax3_s32(s.m1, m8[0], m8[1]), max(m8[2], m8[3]));   // timing probe: tree only
+        s.m1 = __vimax3_s32(s.m1, m8[0], m8[1]);   // timing probe: tree only (results are not a kNN)
         return;
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) unit_event<MASKED>(s, v, j, m8[j], col0 + j * kUnit, slots, pub, nbase, t_cnt);
+    for (int j = 0; j < 2; ++j) unit_event<MASKED>(s, v, j, m8[j], col0 + j * kUnit, slots, pub, nbase, t_cnt);
 }
 
 struct SmemLayout {
@@ -374,7 +374,6 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
     constexpr int kMmaWarp = kEpiWarps + 1;
     constexpr int kHalves = kEpiWarps / 8;             // threads (column ranges) per query row
     constexpr int kColsPerThread = kTileN / kHalves;   // columns of each train tile per thread
-    constexpr int kChunks = kColsPerThread / 32;
     if (!force && ((*static_cast<volatile const int32_t*>(flags) != 0) == FOLD)) return;
 
     extern __shared__ uint8_t smem_raw[];
@@ -567,32 +566,47 @@ knn2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CU
                 const uint32_t taddr = lane_addr + tp.stage * kTmemColsPerStage;
                 const bool partial = FOLD && (t + 1) * kTileN > t_cnt;
                 if (FOLD && kHalves == 2) sk.thr = max(sk.thr, static_cast<int>(lds32(other_pub)));
-                uint32_t v[2][32];
-                tmem_ld_32x32(taddr, v[0]);
+                if (!FOLD) {
+                    uint32_t v[2][32];
+                    tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-                for (int c = 0; c < kChunks; ++c) {
-                    const int col0 = t * kTileN + colbase + c * 32;
-                    int4 nb[8];
-                    if (!FOLD) {
+                    for (int c = 0; c < kColsPerThread / 32; ++c) {
+                        const int col0 = t * kTileN + colbase + c * 32;
+                        int4 nb[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j)
                             nb[j] = __ldg(reinterpret_cast<const int4*>(nbase) + col0 / 4 + j);
-                    }
-                    tmem_ld_wait();
-                    if (c + 1 < kChunks) {
-                        tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
-                    } else {
-                        // every column of this thread is in registers: hand the accumulator back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(empty);
-                    }
-                    if (!FOLD) {
+                        tmem_ld_wait();
+                        if (c + 1 < kColsPerThread / 32) {
+                            tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+                        } else {
+                            // every column of this thread is in registers: hand the accumulator back
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(empty);
+                        }
                         top2_chunk(s, v[c & 1], nb, col0);
-                    } else if (partial) {
-                        fold_chunk<true, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
-                    } else {
-                        fold_chunk<false, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
+                    }
+                } else {
+                    // 16-column chunks, double-buffered: 32 live accumulator registers per thread
+                    uint32_t v[2][16];
+                    tmem_ld_32x16(taddr, v[0]);
+#pragma unroll
+                    for (int c = 0; c < kColsPerThread / 16; ++c) {
+                        const int col0 = t * kTileN + colbase + c * 16;
+                        tmem_ld_wait();
+                        if (c + 1 < kColsPerThread / 16) {
+                            tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
+                        } else {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(empty);
+                        }
+                        if (partial) {
+                            fold_chunk<true, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
+                        } else {
+                            fold_chunk<false, MODE>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
+                        }
                     }
                 }
                 tp.advance();

@@ -27,7 +27,7 @@ ops = 256.0 * 8192 * 8192 * len(pairs)
 for mode, pf in ((4, 0), (3, 0), (3, 2), (2, 0), (1, 0)):
     ctx.set_knn_mode(mode)
     ctx.set_knn_probe_flags(pf)
-    for (w, e) in [(0, 0)]:
+    for (w, e) in ([(0, 0), (2000, 200), (2000, 2000), (20000, 20000)] if mode == 2 else [(0, 0)]):
         ctx.set_knn_waits(w, e)
         ctx.knn2(pairs, ro, buf)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -37,5 +37,5 @@ for mode, pf in ((4, 0), (3, 0), (3, 2), (2, 0), (1, 0)):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 3
-        out[f"mode{mode}_pf{pf}_tops"] = round(ops / (ms * 1e-3) / 1e12, 1)
+        out[f"mode{mode}_pf{pf}_w{w}_e{e}_tops"] = round(ops / (ms * 1e-3) / 1e12, 1)
 print(json.dumps(out))
