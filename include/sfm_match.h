@@ -204,6 +204,11 @@ SFM_API int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32
  * `train_image`, written to d_out i32 [128,128]. */
 SFM_API int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_t tile,
                         int32_t* d_out, void* stream);
+/* Debug: folded accumulators of one 128 x 256 tile through the wide kernel's path
+ * (sfm_b200/csrc/knn_wide.cu: N = 256 MMAs, fold operand as SWIZZLE_32B rows):
+ * a.b + 2016029 - floor(||b||^2 / 2) for query rows q_row.. against descriptor rows t_row..,
+ * written to d_out i32 [128,256]. */
+SFM_API int sfm_debug_wide_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
 /* TMEM read-rate probe: every SM runs `warps` warps issuing `iters` tcgen05.ld each
  * (variant 0: 32x32b.x32 + wait each; 1: .x32, wait every 4; 2: .x64 + wait each;
  * 3: 16x256b.x8, wait every 4); *h_cycles = slowest warp's SM cycles (synchronises). */
@@ -214,10 +219,11 @@ SFM_API int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant
  * back (needs bit 0 and consumers >= 1); bit 2: one extra commit per step.  *ms = elapsed. */
 SFM_API int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc, int32_t flags,
                                   int32_t consumers, float* ms, void* stream);
-/* Select the kNN kernel variant used by sfm_knn2: 0 automatic (norm term folded
- * into the contraction unless a registered row has ||b||^2 > 4,032,059, then the
- * generic variant), 1 generic only, 2 folded only; timing probes whose output is NOT
- * a kNN: 3 folded fast path only, 4 folded TMA + MMA pipeline without an epilogue. */
+/* Select the kNN kernel variant used by sfm_knn2: 0 automatic (wide folded kernel, N = 256
+ * MMAs with the norm term folded into the contraction, unless a registered row has
+ * ||b||^2 > 4,032,059, then the generic variant), 1 generic only, 2 N = 128 folded kernel only,
+ * 5 wide folded kernel only; timing probes whose output is NOT a kNN: 3 / 6 max tree only
+ * (N = 128 / wide), 4 / 7 TMA + MMA pipeline without an epilogue. */
 SFM_API int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode);
 /* mbarrier suspend-time hints (ns; 0 = spin) of the kNN kernel's producer/MMA warps and of
  * its epilogue warps.  Tuning knob; results do not depend on it. */

@@ -56,11 +56,14 @@ struct sfm_ctx {
     int64_t pad_total = 0;
     std::vector<int64_t> h_off, h_pad, h_x;
     CUtensorMap tmap, tmap_x;
+    CUtensorMap tmap_x32, tmap_ax32;   // wide kNN variant: fold operands as 32-byte rows (knn_wide.cu)
+    DevBuf<uint8_t> d_bias32;
     bool have_tmap = false;
     DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
     DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
+    int knn_auto = 0;            // what mode 0 resolves to: 0 = knn.cu fold + generic, 5 = wide fold + generic
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
@@ -206,6 +209,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_x_off.release();
     ctx->d_flags.release();
     ctx->d_bias.release();
+    ctx->d_bias32.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
     ctx->d_work.release();
@@ -258,6 +262,7 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     SFM_CUDA(ctx, ctx->d_x_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_flags.reserve(4));
     SFM_CUDA(ctx, ctx->d_bias.reserve(static_cast<size_t>(x_rows) * SFM_DESC_DIM));
+    SFM_CUDA(ctx, ctx->d_bias32.reserve(static_cast<size_t>(total + SFM_TTILE) * 32));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_x_off.p, ctx->h_x.data(), sizeof(int64_t) * (n_images + 1),
                                   cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
@@ -281,10 +286,24 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
                         estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (bias) failed: CUresult %d", int(r));
+        // wide variant: u8 [128 + total, 32], 256-row boxes (train tile) and a 128-row box (constant rows)
+        const cuuint64_t wdim[2] = {32, static_cast<cuuint64_t>(total + SFM_TTILE)};
+        const cuuint64_t wstride[1] = {32};
+        const cuuint32_t wbox[2] = {32, 256};
+        const cuuint32_t abox[2] = {32, 128};
+        r = ctx->encode(&ctx->tmap_x32, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_bias32.p, wdim, wstride, wbox,
+                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = ctx->encode(&ctx->tmap_ax32, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_bias32.p, wdim, wstride, abox,
+                            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (bias32) failed: CUresult %d", int(r));
         ctx->have_tmap = true;
     }
     sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, ctx->d_x_off.p, n_images,
                       ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_bias.p, ctx->d_flags.p, st, &ctx->launches);
+    sfm::launch_bias32(ctx->d_norms.p, total, ctx->d_bias32.p, ctx->d_flags.p, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     return 0;
 }
@@ -316,9 +335,19 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
     sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
                            ctx->d_x_off.p, ctx->d_work.p, st, &ctx->launches);
-    int r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
-                             ctx->d_norms_pad.p, ctx->d_flags.p, ctx->knn_mode, ctx->knn_tuning, d_knn, ctx->num_sms, st,
-                             &ctx->launches);
+    // knn_mode 0: wide folded kernel, or the generic one when a norm is beyond the fold range (both are
+    // launched; the one that does not apply exits at its first instruction).  1: generic, 2-4: N = 128
+    // folded kernel and its probes (knn.cu), 5: wide only, 6/7: wide timing probes.
+    const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
+    int r = 0;
+    if (km >= 5)
+        r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_work.p, n_work, ctx->d_norms.p,
+                                  ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
+                                  ctx->knn_tuning.probe_flags, d_knn, ctx->num_sms, st, &ctx->launches);
+    if (!r && km <= 5 && !(km == 5 && ctx->knn_mode != 0))
+        r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
+                             ctx->d_norms_pad.p, ctx->d_flags.p, km == 5 ? 9 : km, ctx->knn_tuning, d_knn,
+                             ctx->num_sms, st, &ctx->launches);
     if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     return 0;
 }
@@ -504,6 +533,18 @@ int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_
     return 0;
 }
 
+int sfm_debug_wide_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream) {
+    if (!ctx) return 1;
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
+    if (!d_out) return ctx->fail("d_out is NULL");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    int r = sfm::launch_debug_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, static_cast<int32_t>(q_row),
+                                   static_cast<int32_t>(t_row), d_out, static_cast<cudaStream_t>(stream),
+                                   &ctx->launches);
+    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
 int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant, int32_t iters, int64_t* h_cycles,
                             void* stream) {
     if (!ctx) return 1;
@@ -553,7 +594,7 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (mode < 0 || mode > 4) return ctx->fail("knn mode must be 0..4");
+    if (mode < 0 || mode > 7) return ctx->fail("knn mode must be 0..7");
     ctx->knn_mode = mode;
     return 0;
 }

@@ -44,6 +44,16 @@ int launch_debug_dot(const CUtensorMap& tmap, const CUtensorMap& tmap_x, int32_t
                      int32_t x_row, int32_t x_chunk, int32_t* d_out, cudaStream_t st, int64_t* launches);
 int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t st, int64_t* launches);
 
+// ---- knn_wide.cu (N = 256 folded kernel; fold operands as u8 [128 + R, 32])
+void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32, int32_t* d_flags,
+                   cudaStream_t st, int64_t* launches);
+int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
+                     const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
+                     int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_knn, int num_sms,
+                     cudaStream_t st, int64_t* launches);
+int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
+                      int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches);
+
 // ---- probes.cu
 int launch_tmem_ld_probe(int warps, int variant, int iters, int num_sms, long long* d_out, cudaStream_t st,
                          int64_t* launches);

@@ -980,7 +980,7 @@ int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_
                                        tn, d_knn, grid, st);
         ++*launches;
     }
-    if (e == cudaSuccess && (mode == 0 || mode == 1)) {
+    if (e == cudaSuccess && (mode == 0 || mode == 1 || mode == 9)) {   // 9: generic, only if the flag is raised
         e = launch_knn2_variant<kGeneric>(tmap, tmap_x, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags,
                                           mode == 1, tn, d_knn, grid, st);
         ++*launches;

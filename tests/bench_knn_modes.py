@@ -12,7 +12,7 @@ sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from sfm_b200 import lib as L, synth  # noqa: E402
 
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 36
-modes = [int(m) for m in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 3]
+modes = [int(m) for m in sys.argv[2].split(",")] if len(sys.argv) > 2 else [2, 5, 6, 7]
 s = synth.make_image_set(n_img, 8192, seed=synth.BASE_SEED + 1, device="cuda", tie_frac=0.01)
 ctx = L.Context(0)
 ctx.set_images(s.desc, s.kps, s.offsets.numpy())
@@ -35,7 +35,7 @@ for mode in modes:
     ms = e0.elapsed_time(e1) / 5
     out[f"mode{mode}_ms"] = ms
     out[f"mode{mode}_tops"] = ops / (ms * 1e-3) / 1e12
-    if mode in (1, 2):
+    if mode in (1, 2, 5):
         if ref is None:
             ref = buf.clone()
         else:

@@ -185,10 +185,27 @@ def test_fold_step_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
-@pytest.mark.parametrize("mode", [1, 2])
+def test_wide_fold_tile_accumulators(ctx):
+    """Wide kernel path (N = 256 MMAs, fold operand as SWIZZLE_32B 32-byte rows): accumulators of a
+    128 x 256 tile must equal a.b + C - (||b||^2 >> 1) exactly for every in-range row/column."""
+    descs = _sift_like([300, 1500, 700], 31)
+    off = register(ctx, descs)
+    total = int(off[-1])
+    allrows = np.concatenate(descs).astype(np.int64)
+    for q_row, t_row in [(0, 300), (100, 300 + 512), (1800 + 131, 300 + 1024), (300 + 640, 1800), (7, 0),
+                         (0, total - 200)]:
+        got = ctx.debug_wide_tile(q_row, t_row).cpu().numpy()
+        a = allrows[q_row:q_row + 128]
+        b = allrows[t_row:t_row + 256]
+        want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
+        assert np.array_equal(got[:len(a), :len(b)], want)
+
+
+@pytest.mark.parametrize("mode", [1, 2, 5])
 def test_knn_variants_match_oracle(ctx, mode):
-    """Generic (1) and folded (2) kernels, forced, on SIFT-like data with partial tiles and ties."""
-    sizes = [1, 2, 5, 127, 128, 129, 383, 512, 513, 640, 1025, 2000]
+    """Generic (1), N = 128 folded (2) and wide folded (5) kernels, forced, on SIFT-like data with
+    partial tiles and ties."""
+    sizes = [1, 2, 5, 127, 128, 129, 255, 256, 257, 383, 512, 513, 640, 1025, 2000]
     descs = _sift_like(sizes, 32)
     register(ctx, descs)
     ctx.set_knn_mode(mode)
