@@ -63,7 +63,7 @@ struct sfm_ctx {
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
     DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
-    int knn_auto = 0;            // what mode 0 resolves to: 0 = knn.cu fold + generic, 5 = wide fold + generic
+    int knn_auto = 5;            // what mode 0 resolves to: 0 = knn.cu fold + generic, 5 = wide fold + generic
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
@@ -341,7 +341,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     if (km >= 5)
-        r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_work.p, n_work, ctx->d_norms.p,
+        r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
                                   ctx->knn_tuning.probe_flags, d_knn, ctx->num_sms, st, &ctx->launches);
     if (!r && km <= 5 && !(km == 5 && ctx->knn_mode != 0))
@@ -601,7 +601,7 @@ int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
 
 int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags) {
     if (!ctx) return 1;
-    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 3u;
+    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 7u;
     return 0;
 }
 

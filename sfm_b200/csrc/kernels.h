@@ -48,7 +48,8 @@ int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t s
 void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32, int32_t* d_flags,
                    cudaStream_t st, int64_t* launches);
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
-                     const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
+                     const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
+                     const int32_t* d_norms_pad,
                      int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_knn, int num_sms,
                      cudaStream_t st, int64_t* launches);
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,

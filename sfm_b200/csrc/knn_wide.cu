@@ -46,18 +46,18 @@ constexpr int kEpiWarps = 16;                        // 2 accumulators x 4 lane 
 constexpr int kThreads = (kEpiWarps + 2) * 32;
 constexpr int kColsPerThread = kTileN / 2;           // 128 columns of every tile per thread
 constexpr uint32_t kIdesc = make_idesc_u8(kTileM, kTileN);
-constexpr int kNegV = -(1 << 28);
 constexpr int kFoldC = 255 * 31 * 255 + 254;
 
 constexpr int kUnit = 16;
 constexpr uint32_t kSlotRow = kEpiWarps * 32 * 16;          // bytes between a thread's uint4s
 constexpr uint32_t kSlotStride = (kUnit / 4) * kSlotRow;    // bytes per slot
 constexpr size_t kSlotBytes = 2 * size_t(kSlotStride);      // 64 KiB
+constexpr int kFlagged = -2;                                // out[row].x of a row left to knn_fix_kernel
 constexpr size_t kXchgBytes = 2 * SFM_QBLOCK * 16 + kEpiWarps * 32 * 4;
 constexpr size_t kSmemData = size_t(kAStages) * kABlockBytes + size_t(kBStages) * kStageBytes + kAxBytes +
                              kSlotBytes + kXchgBytes;
 constexpr int kNumBars = 2 * kAStages + 2 * kBStages + 2 * kATiles + 1;
-constexpr size_t kSmemBytes = kSmemData + kNumBars * 8 + 16 + 1024;
+constexpr size_t kSmemBytes = kSmemData + kNumBars * 8 + 16;   // the dynamic window itself is 1024-aligned (checked)
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
 struct Pipe {
@@ -85,13 +85,28 @@ __device__ __forceinline__ uint64_t make_kmajor_sw32_desc(uint32_t smem_addr) {
     return d;
 }
 
-// ---- folded epilogue state (see knn.cu for the derivation; units are 16 columns here)
-struct Cand {
-    int m1, m2;   // units: largest / second largest unit maximum.   exact: k1 / entry threshold on v
-    int c1, c2;   // units: first column of those units (-1: none).  exact: i1 / i2
-    int s1;       // units: shared-memory slot (0/1) of unit c1.     exact: 2
-    int x;        //                                                  exact: k2
-    int thr;      // entry threshold on a unit maximum
+// ---- folded epilogue: branch-free tracking of the best 16-column units per thread.
+// The exact ranking key is K = 2 a.b - ||b||^2 = 2 (v - C) - p (maximised), v the folded
+// accumulator (0 <= v < 2^23) and p the parity of ||b||^2.  Both nearest neighbours have v >= V2,
+// the second largest v of the row, so they lie in units whose maximum m is >= m2, the second
+// largest UNIT maximum (m2 <= V2).  Per unit a thread forms one packed u32 key
+//     [ m >> sh | uidrev : ubits | slot : 1 ],   uidrev = (units of the work item - 1) - unit index
+// (an earlier unit wins on equal m) and keeps the four largest keys k1 >= k2 >= dm >= dd with a
+// min/max insertion network.  The units of k1 and k2 are PARKED: when a key enters the top two its
+// 16 accumulators are stored to shared-memory slot `slot`, the slot of the key it evicts (k2).
+// At the end of the work item the parked values give the exact top-2 (resolve_units).  A third
+// unit can only matter if its (truncated) maximum equals k2's: then dm names it and its 16 keys
+// are recomputed from the descriptors (recompute_unit, ~2 % of rows); if dd ties as well the row
+// is flagged for knn_fix_kernel (brute force).  ubits / sh depend on the train image size:
+// 8192 rows need 8 bits and no truncation, 32768 rows 10 bits and sh = 2 (ties on the truncated
+// maximum are merely more frequent; the logic above is exact for any monotone truncation).
+struct Trk {
+    uint32_t k1, k2, dm, dd;
+};
+
+struct KeyFmt {
+    uint32_t sh, mul, ubits;   // key = (m >> sh) * mul + (uidrev << 1) + slot, mul = 2^(ubits+1)
+    int n_units;               // units per thread over the whole work item (8 per train tile)
 };
 
 struct Top2K {
@@ -116,17 +131,77 @@ __device__ __forceinline__ bool key_before(int ka, int ia, int kb, int ib) {
     return ka > kb || (ka == kb && ia < ib);
 }
 
+// Insert under the full (key desc, index asc) order (columns arrive in any order).
+__device__ __forceinline__ void top2k_insert_ordered(Top2K& s, int key, int col) {
+    if (s.i1 < 0 || key_before(key, col, s.k1, s.i1)) {
+        s.k2 = s.k1;
+        s.i2 = s.i1;
+        s.k1 = key;
+        s.i1 = col;
+    } else if (s.i2 < 0 || key_before(key, col, s.k2, s.i2)) {
+        s.k2 = key;
+        s.i2 = col;
+    }
+}
+
+// 16 folded accumulators of one row = one unit, chunk c of its tile; ut = uidrev << 1 of chunk 0.
+// MASKED: columns >= t_cnt (last, partial train tile) count as v = 0 (real accumulators are >= 0;
+// resolve_units skips them by column).  TREE_ONLY: timing probe.
+template <bool MASKED, bool TREE_ONLY>
+__device__ __forceinline__ void fold_chunk(Trk& s, const uint32_t (&acc)[16], int col0, int t_cnt,
+                                           uint32_t slots, const KeyFmt& kf, uint32_t ut, uint32_t c) {
+    int v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        v[e] = static_cast<int>(acc[e]);
+        if (MASKED) v[e] = (col0 + e < t_cnt) ? v[e] : 0;
+    }
+    const int a0 = __vimax3_s32(v[0], v[1], v[2]), a1 = __vimax3_s32(v[3], v[4], v[5]);
+    const int a2 = __vimax3_s32(v[6], v[7], v[8]), a3 = __vimax3_s32(v[9], v[10], v[11]);
+    const int a4 = __vimax3_s32(v[12], v[13], v[14]);
+    const int m = max(__vimax3_s32(a0, a1, a2), __vimax3_s32(a3, a4, v[15]));
+    if (TREE_ONLY) {
+        s.k1 = max(s.k1, static_cast<uint32_t>(m));
+        return;
+    }
+    const uint32_t sb = s.k2 & 1u;
+    const uint32_t key = (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + ut + (sb - 2u * c);
+    if (key > s.k2) {
+        const uint32_t dst = slots + sb * kSlotStride;
+#pragma unroll
+        for (int g = 0; g < kUnit / 4; ++g)
+            sts128(dst + g * kSlotRow, v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+    }
+    const uint32_t t1 = min(s.k1, key);
+    s.k1 = max(s.k1, key);
+    const uint32_t t2 = min(s.k2, t1);
+    s.k2 = max(s.k2, t1);
+    const uint32_t t3 = min(s.dm, t2);
+    s.dm = max(s.dm, t2);
+    s.dd = max(s.dd, t3);
+}
+
+// First train column of the unit a key names (colbase: first column of this thread's half).
+__device__ __forceinline__ int key_col(uint32_t key, const KeyFmt& kf, int colbase) {
+    const int uidrev = static_cast<int>((key >> 1) & ((1u << kf.ubits) - 1u));
+    const int idx = kf.n_units - 1 - uidrev;
+    return (idx >> 3) * kTileN + colbase + (idx & 7) * kUnit;
+}
+
 // Exact top-2 of the (at most) two parked units, visited in ascending column order.
-__device__ __noinline__ Top2K resolve_units(Cand s, uint32_t slots, const int32_t* __restrict__ nbase,
-                                            int t_cnt) {
+__device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const KeyFmt& kf, int colbase,
+                                               uint32_t slots, const int32_t* __restrict__ nbase, int t_cnt) {
     Top2K r{INT_MIN, INT_MIN, -1, -1};
-    const bool second_first = s.c2 >= 0 && s.c2 < s.c1;
+    const int s1 = s.k1 & 1, s2 = s.k2 & 1;
+    const int c1 = n_seen >= 1 ? key_col(s.k1, kf, colbase) : -1;
+    const int c2 = n_seen >= 2 ? key_col(s.k2, kf, colbase) : -1;
+    const bool second_first = c2 >= 0 && c2 < c1;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         const bool take2 = (pass == 0) == second_first;
-        const int c = take2 ? s.c2 : s.c1;
+        const int c = take2 ? c2 : c1;
         if (c < 0) continue;
-        const uint32_t src = slots + (take2 ? (s.s1 ^ 1) : s.s1) * kSlotStride;
+        const uint32_t src = slots + (take2 ? s2 : s1) * kSlotStride;
 #pragma unroll
         for (int g = 0; g < kUnit / 4; ++g) {
             const uint4 q = lds128(src + g * kSlotRow);
@@ -144,101 +219,40 @@ __device__ __noinline__ Top2K resolve_units(Cand s, uint32_t slots, const int32_
     return r;
 }
 
-struct UnitVals {
-    int v[kUnit];
-};
-
-// Rare path: element-wise exact update of one row with one unit (switching the row to exact
-// mode first if it was still tracking units).
-__device__ __noinline__ Cand exact_unit(Cand s, UnitVals in, int col, uint32_t slots,
-                                        const int32_t* __restrict__ nbase, int t_cnt) {
-    Top2K r;
-    if (s.s1 < 2) {
-        r = resolve_units(s, slots, nbase, t_cnt);
-    } else {
-        r = Top2K{s.m1, s.x, s.c1, s.c2};
-    }
+// Rare path: the exact keys of one dropped unit, recomputed from the descriptors on the CUDA
+// cores and merged under the (key desc, index asc) order.
+__device__ __noinline__ Top2K recompute_unit(Top2K r, const uint8_t* __restrict__ desc, int q_abs, int t_row,
+                                             int col, int t_cnt, const int32_t* __restrict__ nbase) {
+    uint4 a[8];
 #pragma unroll
-    for (int g = 0; g < kUnit / 4; ++g) {
-        const int4 nb = __ldg(reinterpret_cast<const int4*>(nbase + col) + g);
-        const int pp[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
+    for (int i = 0; i < 8; ++i)
+        a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_abs) * kRowBytes) + i);
+#pragma unroll 1
+    for (int e = 0; e < kUnit; ++e) {
+        const int c = col + e;
+        if (c >= t_cnt) break;
+        const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes);
+        uint32_t dot = 0;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int c = col + 4 * g + e;
-            if (c < t_cnt) top2k_insert(r, 2 * in.v[4 * g + e] - (pp[e] + 2 * kFoldC), c);
+        for (int i = 0; i < 8; ++i) {
+            const uint4 b = __ldg(bp + i);
+            dot = __dp4a(a[i].x, b.x, dot);
+            dot = __dp4a(a[i].y, b.y, dot);
+            dot = __dp4a(a[i].z, b.z, dot);
+            dot = __dp4a(a[i].w, b.w, dot);
         }
+        top2k_insert_ordered(r, 2 * static_cast<int>(dot) - __ldg(nbase + c), c);
     }
-    s.m1 = r.k1;
-    s.x = r.k2;
-    s.c1 = r.i1;
-    s.c2 = r.i2;
-    s.s1 = 2;
-    s.m2 = (r.k2 >> 1) + 1 + kFoldC;   // v can enter iff 2 (v - C) - p > k2 for some parity p
-    return s;
-}
-
-// One unit whose maximum m reached the row's threshold.  `pub`: where this thread publishes
-// its bound for the row's other thread (m2 in unit mode; threshold - 1 in exact mode, because an
-// element one below it can still tie this thread's second key and win on the lower index).
-__device__ __forceinline__ void unit_event(Cand& s, const int (&v)[kUnit], int m, int col, uint32_t slots,
-                                           uint32_t pub, const int32_t* __restrict__ nbase, int t_cnt) {
-    const bool new_best = m > s.m1;
-    // a unit with maximum == m2 would stay unparked: the incoming one, or the evicted second
-    const bool tie = m == s.m2 || (new_best && s.m2 == s.m1 && s.c2 >= 0);
-    if (s.s1 < 2 && !tie) {
-        const uint32_t dst = slots + (s.s1 ^ 1) * kSlotStride;
-#pragma unroll
-        for (int g = 0; g < kUnit / 4; ++g)
-            sts128(dst + g * kSlotRow, v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
-        if (new_best) {
-            s.m2 = s.m1;
-            s.c2 = s.c1;
-            s.m1 = m;
-            s.c1 = col;
-            s.s1 ^= 1;
-        } else {
-            s.m2 = m;
-            s.c2 = col;
-        }
-    } else {
-        UnitVals in;
-#pragma unroll
-        for (int e = 0; e < kUnit; ++e) in.v[e] = v[e];
-        s = exact_unit(s, in, col, slots, nbase, t_cnt);
-    }
-    s.thr = max(s.thr, s.m2);
-    sts32(pub, static_cast<uint32_t>(s.s1 == 2 ? s.m2 - 1 : s.m2));
-}
-
-// 16 folded accumulators of one row = one unit.  MASKED: columns >= t_cnt (last, partial train
-// tile) are forced to kNegV.  TREE_ONLY: timing probe (max tree, no candidate tracking).
-template <bool MASKED, bool TREE_ONLY>
-__device__ __forceinline__ void fold_chunk(Cand& s, const uint32_t (&acc)[16], int col0, int t_cnt,
-                                           uint32_t slots, uint32_t pub, const int32_t* __restrict__ nbase) {
-    int v[16];
-#pragma unroll
-    for (int e = 0; e < 16; ++e) {
-        v[e] = static_cast<int>(acc[e]);
-        if (MASKED) v[e] = (col0 + e < t_cnt) ? v[e] : kNegV;
-    }
-    const int a0 = __vimax3_s32(v[0], v[1], v[2]), a1 = __vimax3_s32(v[3], v[4], v[5]);
-    const int a2 = __vimax3_s32(v[6], v[7], v[8]), a3 = __vimax3_s32(v[9], v[10], v[11]);
-    const int a4 = __vimax3_s32(v[12], v[13], v[14]);
-    const int m = max(__vimax3_s32(a0, a1, a2), __vimax3_s32(a3, a4, v[15]));
-    if (TREE_ONLY) {
-        s.m1 = max(s.m1, m);
-        return;
-    }
-    if (m >= s.thr && (!MASKED || m > kNegV)) unit_event(s, v, m, col0, slots, pub, nbase, t_cnt);
+    return r;
 }
 
 struct SmemLayout {
     uint8_t* a;      // kAStages x (2 x 128 query rows x 128 B)
     uint8_t* b;      // kBStages x (256 train rows x 128 B | 256 x 32 B fold operand)
     uint8_t* ax;     // constant A operand of the fold step (128 x 32 B)
-    uint4* slots;    // parked candidate units
+    uint4* slots;    // parked candidate units: [slot][4 x uint4][thread]
     uint4* xchg;     // [2][256] per-row results handed from the upper to the lower column half
-    int32_t* pub;    // [512] bound each epilogue thread publishes for its row's other thread
+    int32_t* pub;    // [2][256] tie flag handed over with them
     uint64_t* a_full;
     uint64_t* a_empty;
     uint64_t* b_full;
@@ -248,8 +262,7 @@ struct SmemLayout {
     uint64_t* ax_full;
     uint32_t* tmem_slot;
     __device__ explicit SmemLayout(uint8_t* raw) {
-        uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) &
-                                                   ~static_cast<uintptr_t>(1023));
+        uint8_t* base = raw;   // 1024-aligned (checked at kernel entry): no slack to spare for rounding up
         a = base;
         b = a + size_t(kAStages) * kABlockBytes;
         ax = b + size_t(kBStages) * kStageBytes;
@@ -272,15 +285,16 @@ struct SmemLayout {
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
-                 const __grid_constant__ CUtensorMap tmap_ax, const WorkItem* __restrict__ work,
-                 long long n_work, const int32_t* __restrict__ norms, const int32_t* __restrict__ norms_pad,
+                 const __grid_constant__ CUtensorMap tmap_ax, const uint8_t* __restrict__ desc,
+                 const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms, const int32_t* __restrict__ norms_pad,
                  int32_t* __restrict__ flags, int force, uint32_t probe_flags, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     // flags[0] != 0: some row's norm is beyond the fold range -> the generic kernel runs instead
     if (!force && *static_cast<volatile const int32_t*>(flags) != 0) return;
 
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    if (smem_u32(smem_raw) & 1023u) __trap();   // SWIZZLE_128B tiles need 1024-byte alignment
     SmemLayout sm(smem_raw);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -403,10 +417,6 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         const int colbase = half * kColsPerThread;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kTileN + colbase;
         const uint32_t my_slots = smem_u32(sm.slots) + threadIdx.x * 16;
-        const uint32_t my_pub = smem_u32(sm.pub) + threadIdx.x * 4;
-        const uint32_t other_pub = smem_u32(sm.pub) + (threadIdx.x ^ (8 * 32)) * 4;
-        sts32(my_pub, static_cast<uint32_t>(INT_MIN));
-        asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp & 7)) : "memory");
         uint64_t* full = &sm.t_full[acc];
         uint64_t* empty = &sm.t_empty[acc];
         uint32_t tphase = 0;
@@ -414,14 +424,23 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         for (long long w = blockIdx.x; w < n_work; w += gridDim.x, ++item) {
             const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
             const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
-            const int q_row = w0.x, q_cnt = w0.y, t_cnt = w0.w, t_pad = w1.x;
+            const int q_row = w0.x, q_cnt = w0.y, t_row = w0.z, t_cnt = w0.w, t_pad = w1.x;
             const long long out_row =
                 static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
             const bool valid = row < q_cnt;
             const int na = valid ? __ldg(norms + q_row + row) : 0;
             const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
             const int32_t* nbase = norms_pad + t_pad;
-            Cand sk{INT_MIN, INT_MIN, -1, -1, 0, 0, INT_MIN};
+            KeyFmt kf;
+            kf.n_units = n_tiles * (kColsPerThread / kUnit);
+            kf.ubits = 32 - __clz(kf.n_units - 1);
+            kf.sh = kf.ubits > 8 ? kf.ubits - 8 : 0;   // m < 2^23: (23 - sh) + ubits + 1 <= 32 bits
+            kf.mul = 2u << kf.ubits;
+            // units this thread will see: 8 per full tile, fewer in the last, partial one
+            const int rem = t_cnt - (n_tiles - 1) * kTileN - colbase;
+            const int n_seen = (n_tiles - 1) * (kColsPerThread / kUnit) +
+                               min(max((rem + kUnit - 1) / kUnit, 0), kColsPerThread / kUnit);
+            Trk sk{1, 0, 0, 0};   // empty keys: k1 owns slot 1, k2 slot 0 (the first unit is parked in slot 0)
             for (int t = 0; t < n_tiles; ++t) {
                 mbar_wait(full, tphase);
                 tc_fence_after();
@@ -432,50 +451,64 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     if (lane == 0) mbar_arrive(empty);
                     continue;
                 }
-                const bool partial = (t + 1) * kTileN > t_cnt;
-                sk.thr = max(sk.thr, static_cast<int>(lds32(other_pub)));
                 // 16-column chunks, double-buffered: 32 live accumulator registers per thread
                 uint32_t v[2][16];
                 tmem_ld_32x16(taddr, v[0]);
+                const uint32_t ut = static_cast<uint32_t>(kf.n_units - 1 - t * (kColsPerThread / kUnit)) << 1;
+                if ((t + 1) * kTileN <= t_cnt) {
 #pragma unroll
-                for (int c = 0; c < kColsPerThread / 16; ++c) {
-                    const int col0 = t * kTileN + colbase + c * 16;
-                    tmem_ld_wait();
-                    if (c + 1 < kColsPerThread / 16) {
-                        tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
-                    } else {
-                        // every column of this thread is in registers: hand the accumulator back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(empty);
+                    for (int c = 0; c < kColsPerThread / 16; ++c) {
+                        tmem_ld_wait();
+                        if (c + 1 < kColsPerThread / 16) {
+                            tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
+                        } else {
+                            // every column of this thread is in registers: hand the accumulator back
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(empty);
+                        }
+                        fold_chunk<false, MODE == 1>(sk, v[c & 1], t * kTileN + colbase + c * 16, t_cnt, my_slots,
+                                                     kf, ut, c);
                     }
-                    if (partial) {
-                        fold_chunk<true, MODE == 1>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
-                    } else {
-                        fold_chunk<false, MODE == 1>(sk, v[c & 1], col0, t_cnt, my_slots, my_pub, nbase);
+                } else {   // last, partial train tile: chunks wholly beyond the image are skipped
+#pragma unroll
+                    for (int c = 0; c < kColsPerThread / 16; ++c) {
+                        const int col0 = t * kTileN + colbase + c * 16;
+                        tmem_ld_wait();
+                        if (c + 1 < kColsPerThread / 16) {
+                            tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
+                        } else {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(empty);
+                        }
+                        if (col0 < t_cnt) fold_chunk<true, MODE == 1>(sk, v[c & 1], col0, t_cnt, my_slots, kf, ut, c);
                     }
                 }
             }
             if (MODE != 0) {
-                if (valid && half == 0) out[out_row + row] = make_int4(sk.m1, sk.m2, na, 0);   // keeps the probe live
+                if (valid && half == 0) out[out_row + row] = make_int4(static_cast<int>(sk.k1), static_cast<int>(sk.k2), na, 0);   // keeps the probe live
                 continue;
             }
-            Top2K r;
-            if (sk.s1 == 2) {
-                r = Top2K{sk.m1, sk.x, sk.c1, sk.c2};
-            } else {
-                r = resolve_units(sk, my_slots, nbase, t_cnt);
-            }
-            const unsigned ex = __ballot_sync(0xffffffffu, valid && sk.s1 == 2);
-            if (ex && lane == 0) atomicAdd(flags + 1, __popc(ex));   // statistics: rows in exact mode
+            Top2K r = resolve_units(sk, n_seen, kf, colbase, my_slots, nbase, t_cnt);
+            // a dropped unit whose (truncated) maximum equals the second kept one may hold a candidate:
+            // the best dropped one is recomputed here, a second one sends the row to knn_fix_kernel
+            const uint32_t mf = kf.ubits + 1;
+            if (valid && n_seen >= 3 && (sk.dm >> mf) == (sk.k2 >> mf))
+                r = recompute_unit(r, desc, q_row + row, t_row, key_col(sk.dm, kf, colbase), t_cnt, nbase);
+            const bool tie = n_seen >= 4 && (sk.dd >> mf) == (sk.k2 >> mf);
             // the thread of the upper column half hands its top-2 to the lower half's thread,
             // which merges under the (key, lowest index) order and writes the row
             const uint32_t xaddr = smem_u32(sm.xchg) + ((item & 1) * SFM_QBLOCK + row) * 16;
-            if (half == 1) sts128(xaddr, r.k1, r.k2, r.i1, r.i2);
-            sts32(my_pub, static_cast<uint32_t>(INT_MIN));   // next work item starts unbounded
+            const uint32_t faddr = smem_u32(sm.pub) + ((item & 1) * SFM_QBLOCK + row) * 4;
+            if (half == 1) {
+                sts128(xaddr, r.k1, r.k2, r.i1, r.i2);
+                sts32(faddr, tie ? 1u : 0u);
+            }
             asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp & 7)) : "memory");
             if (half == 0) {
                 const uint4 o = lds128(xaddr);
+                const bool flagged = tie || lds32(faddr) != 0;
                 Top2K b{static_cast<int>(o.x), static_cast<int>(o.y), static_cast<int>(o.z), static_cast<int>(o.w)};
                 if (b.i1 < 0) b.i1 = INT_MAX;   // empty entries sort last
                 if (b.i2 < 0) b.i2 = INT_MAX;
@@ -495,12 +528,14 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     mrg.k2 = theirs ? b.k2 : r.k1;
                     mrg.i2 = theirs ? b.i2 : r.i1;
                 }
+                const unsigned fl = __ballot_sync(0xffffffffu, valid && flagged);
+                if (fl && lane == 0) atomicAdd(flags + 1, __popc(fl));   // rows left to knn_fix_kernel
                 if (valid) {
                     const int i1 = mrg.i1 == INT_MAX ? -1 : mrg.i1;
                     const int i2 = mrg.i2 == INT_MAX ? -1 : mrg.i2;
                     const int d1 = i1 < 0 ? INT_MAX : na - mrg.k1;
                     const int d2 = i2 < 0 ? INT_MAX : na - mrg.k2;
-                    out[out_row + row] = make_int4(i1, i2, d1, d2);
+                    out[out_row + row] = flagged ? make_int4(kFlagged, kFlagged, 0, 0) : make_int4(i1, i2, d1, d2);
                 }
             }
         }
@@ -547,6 +582,94 @@ __global__ void bias32_kernel(const int32_t* __restrict__ norms, long long total
     uint4* dst = reinterpret_cast<uint4*>(bias + r * kUmmaK);
     dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
     dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+
+// Rows the wide kernel flagged (out[row].x == kFlagged: two dropped units tie with the second kept
+// one) are recomputed here exactly on the CUDA cores.  One block per work item; its flagged rows
+// are taken one at a time by the whole block: threads stride over the train columns (ascending per
+// thread, strict compares), partial top-2s merged under the (key desc, index asc) order = OpenCV's
+// lowest-index tie rule.  flags[1] counts flagged rows since sfm_set_images; while it is 0 every
+// block exits at once.
+__global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __restrict__ work,
+                                                             const uint8_t* __restrict__ desc,
+                                                             const int32_t* __restrict__ norms,
+                                                             const int32_t* __restrict__ flags,
+                                                             int4* __restrict__ out) {
+    if (*(static_cast<volatile const int32_t*>(flags) + 1) == 0) return;
+    __shared__ int s_list[SFM_QBLOCK];
+    __shared__ int s_n;
+    __shared__ Top2K s_part[SFM_QBLOCK / 32];
+    const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + blockIdx.x));
+    const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + blockIdx.x) + 1);
+    const int q_row = w0.x, q_cnt = w0.y, t_row = w0.z, t_cnt = w0.w;
+    const long long out_row =
+        static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    if (static_cast<int>(threadIdx.x) < q_cnt && out[out_row + threadIdx.x].x == kFlagged)
+        s_list[atomicAdd(&s_n, 1)] = threadIdx.x;
+    __syncthreads();
+    const int n = s_n;
+    for (int k = 0; k < n; ++k) {
+        const int r = s_list[k];
+        uint4 a[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_row + r) * kRowBytes) + i);
+        Top2K best{INT_MIN, INT_MIN, INT_MAX, INT_MAX};
+#pragma unroll 2
+        for (int c = threadIdx.x; c < t_cnt; c += SFM_QBLOCK) {
+            const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes);
+            uint32_t dot = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint4 b = __ldg(bp + i);
+                dot = __dp4a(a[i].x, b.x, dot);
+                dot = __dp4a(a[i].y, b.y, dot);
+                dot = __dp4a(a[i].z, b.z, dot);
+                dot = __dp4a(a[i].w, b.w, dot);
+            }
+            top2k_insert(best, 2 * static_cast<int>(dot) - __ldg(norms + t_row + c), c);
+        }
+        auto merge = [](const Top2K& x, const Top2K& y) {
+            Top2K m;
+            if (key_before(x.k1, x.i1, y.k1, y.i1)) {
+                m.k1 = x.k1;
+                m.i1 = x.i1;
+                const bool keep = key_before(x.k2, x.i2, y.k1, y.i1);
+                m.k2 = keep ? x.k2 : y.k1;
+                m.i2 = keep ? x.i2 : y.i1;
+            } else {
+                m.k1 = y.k1;
+                m.i1 = y.i1;
+                const bool keep = key_before(y.k2, y.i2, x.k1, x.i1);
+                m.k2 = keep ? y.k2 : x.k1;
+                m.i2 = keep ? y.i2 : x.i1;
+            }
+            return m;
+        };
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            Top2K b;
+            b.k1 = __shfl_xor_sync(0xffffffffu, best.k1, o);
+            b.k2 = __shfl_xor_sync(0xffffffffu, best.k2, o);
+            b.i1 = __shfl_xor_sync(0xffffffffu, best.i1, o);
+            b.i2 = __shfl_xor_sync(0xffffffffu, best.i2, o);
+            best = merge(best, b);
+        }
+        if (lane == 0) s_part[warp] = best;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            Top2K m = s_part[0];
+            for (int w = 1; w < SFM_QBLOCK / 32; ++w) m = merge(m, s_part[w]);
+            const int na = __ldg(norms + q_row + r);
+            const int i1 = m.i1 == INT_MAX ? -1 : m.i1;
+            const int i2 = m.i2 == INT_MAX ? -1 : m.i2;
+            out[out_row + r] = make_int4(i1, i2, i1 < 0 ? INT_MAX : na - m.k1, i2 < 0 ? INT_MAX : na - m.k2);
+        }
+        __syncthreads();
+    }
 }
 
 // Debug: raw folded accumulators of one 128 x 256 tile through the same TMA / UMMA path.
@@ -614,7 +737,7 @@ debug_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
 
 template <int MODE>
 cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
-                           const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
+                           const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                            const int32_t* d_norms_pad, int32_t* d_flags, int force, uint32_t probe_flags,
                            int32_t* d_knn, unsigned grid, cudaStream_t st) {
     static bool configured = false;
@@ -624,7 +747,7 @@ cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, c
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    knn2_wide_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, tmap_ax, d_work, n_work, d_norms,
+    knn2_wide_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms,
                                                               d_norms_pad, d_flags, force, probe_flags,
                                                               reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
@@ -642,22 +765,29 @@ void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32
 // variant 0: the kNN (exits at once when the fold-range flag is raised, unless force);
 // 1: max tree only, 2: no epilogue (timing probes).
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
-                     const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
+                     const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
+                     const int32_t* d_norms_pad,
                      int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_knn, int num_sms,
                      cudaStream_t st, int64_t* launches) {
     if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
     cudaError_t e;
     if (variant == 1)
-        e = launch_variant<1>(tmap, tmap_x, tmap_ax, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
+        e = launch_variant<1>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
                               d_knn, grid, st);
     else if (variant == 2)
-        e = launch_variant<2>(tmap, tmap_x, tmap_ax, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
+        e = launch_variant<2>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
                               d_knn, grid, st);
     else
-        e = launch_variant<0>(tmap, tmap_x, tmap_ax, d_work, n_work, d_norms, d_norms_pad, d_flags, force,
+        e = launch_variant<0>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, force,
                               probe_flags, d_knn, grid, st);
     ++*launches;
+    if (e == cudaSuccess && variant == 0 && !(probe_flags & 4u)) {   // (probe bit 2: main kernel alone)
+        knn_fix_kernel<<<static_cast<unsigned>(n_work), SFM_QBLOCK, 0, st>>>(d_work, d_desc, d_norms, d_flags,
+                                                                            reinterpret_cast<int4*>(d_knn));
+        ++*launches;
+        e = cudaGetLastError();
+    }
     return static_cast<int>(e);
 }
 

@@ -40,4 +40,17 @@ for mode in modes:
             ref = buf.clone()
         else:
             out[f"mode{mode}_equals_first"] = bool(torch.equal(ref, buf))
+ctx.set_knn_mode(5)
+ctx.set_knn_probe_flags(4)
+for _ in range(2):
+    ctx.knn2(pairs, ro, buf)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(5):
+    ctx.knn2(pairs, ro, buf)
+e1.record()
+torch.cuda.synchronize()
+out["mode5_nofix_tops"] = ops / (e0.elapsed_time(e1) / 5 * 1e-3) / 1e12
+out["flagged_rows_frac"] = float((buf[:, 0] == -2).float().mean().item())
+ctx.set_knn_probe_flags(0)
 print(json.dumps(out))

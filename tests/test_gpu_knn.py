@@ -201,6 +201,22 @@ def test_wide_fold_tile_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
+def test_knn_wide_long_train_images(ctx):
+    """Wide kernel with train images beyond 8192 rows: unit ids need more than 8 key bits, the unit
+    maxima are truncated in the packed keys and ties on the truncated value are recomputed."""
+    sizes = [700, 9000, 20000]
+    descs = _sift_like(sizes, 35)
+    register(ctx, descs)
+    ctx.set_knn_mode(5)
+    try:
+        pairs = [(0, 1), (0, 2), (1, 2)]
+        got, ro = gpu_knn(ctx, pairs)
+    finally:
+        ctx.set_knn_mode(0)
+    for p, (i, j) in enumerate(pairs):
+        check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+
+
 @pytest.mark.parametrize("mode", [1, 2, 5])
 def test_knn_variants_match_oracle(ctx, mode):
     """Generic (1), N = 128 folded (2) and wide folded (5) kernels, forced, on SIFT-like data with
