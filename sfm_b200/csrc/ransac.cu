@@ -27,7 +27,7 @@ namespace sfm {
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 128;   // 4 CTAs per SM: the per-pair phases are latency chains, residency hides them
 constexpr int kWarps = kThreads / 32;
 constexpr int kChunk = 2048;   // staged correspondences per pass (32 KiB)
 constexpr int kMinSample = 8;
@@ -36,6 +36,7 @@ struct Shared {
     float4 pts[kChunk];
     double red[kWarps][48];
     double res[48];
+    double jA[9][9], jV[9][9];   // warp-cooperative Jacobi of the refit (warp_refit_from_normal)
     double Fd[9];
     float bestF[9];
     float warpF[kWarps][9];
@@ -106,6 +107,66 @@ __device__ __forceinline__ float symmetric_error(const double (&F)[9], float x1,
     return __fmul_rn(__fadd_rn(e1, e2), 0.5f);
 }
 
+// refit_from_normal (ransac_core.h) with the 9x9 cyclic Jacobi run by one warp: the same rotation
+// sequence and the same arithmetic per element, lane k updating row/column entry k of A and lane
+// 9 + k that of V, instead of one thread walking dynamically indexed local arrays (that serial
+// eigen-solve was 40 % of the kernel).  Called by warp 0 only; result in F (all lanes).
+__device__ bool warp_refit_from_normal(const double (&ata)[45], double c1x, double c1y, double s1, double c2x,
+                                       double c2y, double s2, Shared& sh, double (&F)[9]) {
+    const int lane = threadIdx.x & 31;
+    for (int idx = lane; idx < 81; idx += 32) {
+        const int i = idx / 9, j = idx % 9;
+        const int r = i < j ? i : j, c = i < j ? j : i;
+        sh.jA[i][j] = ata[r * 9 - r * (r - 1) / 2 + (c - r)];
+        sh.jV[i][j] = i == j ? 1.0 : 0.0;
+    }
+    __syncwarp();
+    for (int sweep = 0; sweep < 12; ++sweep) {
+        double off = 0, diag = 0;
+        for (int i = 0; i < 9; ++i) {
+            diag += sh.jA[i][i] * sh.jA[i][i];
+            for (int j = i + 1; j < 9; ++j) off += sh.jA[i][j] * sh.jA[i][j];
+        }
+        if (off <= 1e-30 * diag) break;
+        for (int p = 0; p < 8; ++p)
+            for (int q = p + 1; q < 9; ++q) {
+                const double apq = sh.jA[p][q];
+                if (apq == 0.0) continue;
+                const double theta = (sh.jA[q][q] - sh.jA[p][p]) / (2.0 * apq);
+                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+                __syncwarp();
+                if (lane < 9) {
+                    const double akp = sh.jA[lane][p], akq = sh.jA[lane][q];
+                    sh.jA[lane][p] = c * akp - s * akq;
+                    sh.jA[lane][q] = s * akp + c * akq;
+                } else if (lane < 18) {
+                    const int k = lane - 9;
+                    const double vkp = sh.jV[k][p], vkq = sh.jV[k][q];
+                    sh.jV[k][p] = c * vkp - s * vkq;
+                    sh.jV[k][q] = s * vkp + c * vkq;
+                }
+                __syncwarp();
+                if (lane < 9) {
+                    const double apk = sh.jA[p][lane], aqk = sh.jA[q][lane];
+                    sh.jA[p][lane] = c * apk - s * aqk;
+                    sh.jA[q][lane] = s * apk + c * aqk;
+                }
+                __syncwarp();
+            }
+    }
+    int m = 0;
+    for (int i = 1; i < 9; ++i)
+        if (sh.jA[i][i] < sh.jA[m][m]) m = i;
+    for (int i = 0; i < 9; ++i) F[i] = sh.jV[i][m];
+    rc::enforce_rank2<double>(F);
+    rc::denormalise<double>(F, c1x, c1y, s1, c2x, c2y, s2);
+    rc::scale_unit<double>(F);
+    bool ok = true;
+    for (int i = 0; i < 9; ++i) ok = ok && (fabs(F[i]) <= 1.0);
+    return ok;
+}
+
 __device__ void write_skip(int p, int m, int status, double* F_out, sfm_pair_metrics* metrics,
                            int32_t* status_out) {
     if (threadIdx.x < 9 && F_out) F_out[9ll * p + threadIdx.x] = 0.0;
@@ -124,7 +185,7 @@ __device__ void write_skip(int p, int m, int status, double* F_out, sfm_pair_met
     }
 }
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
 ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32_t* __restrict__ cnt,
                      const int32_t* __restrict__ pair_ids, const float* __restrict__ pts1,
                      const float* __restrict__ pts2, const double* __restrict__ F_in,
@@ -297,24 +358,25 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                     }
                 }
                 block_sum<47>(acc, sh);
-                if (threadIdx.x == 0) {
-                    sh.flag = 0;
-                    if (acc[45] > 1e-9 && acc[46] > 1e-9) {
-                        const double s1 = 1.4142135623730951 * n_in / acc[45];
-                        const double s2 = 1.4142135623730951 * n_in / acc[46];
-                        const double wgt[9] = {s1 * s2, s1 * s2, s2, s1 * s2, s1 * s2, s2, s1, s1, 1.0};
-                        double ata[45];
-                        int k = 0;
-                        for (int r = 0; r < 9; ++r)
-                            for (int c = r; c < 9; ++c) {
-                                ata[k] = acc[k] * wgt[r] * wgt[c];
-                                ++k;
-                            }
-                        double Fn[9];
-                        if (rc::refit_from_normal(ata, c1x, c1y, s1, c2x, c2y, s2, Fn)) {
-                            for (int i = 0; i < 9; ++i) sh.res[i] = Fn[i];
-                            sh.flag = 1;
+                if (threadIdx.x == 0) sh.flag = 0;
+                if (warp == 0 && acc[45] > 1e-9 && acc[46] > 1e-9) {
+                    const double s1 = 1.4142135623730951 * n_in / acc[45];
+                    const double s2 = 1.4142135623730951 * n_in / acc[46];
+                    const double wgt[9] = {s1 * s2, s1 * s2, s2, s1 * s2, s1 * s2, s2, s1, s1, 1.0};
+                    double ata[45];
+                    int k = 0;
+#pragma unroll
+                    for (int r = 0; r < 9; ++r)
+#pragma unroll
+                        for (int c = r; c < 9; ++c) {
+                            ata[k] = acc[k] * wgt[r] * wgt[c];
+                            ++k;
                         }
+                    double Fn[9];
+                    const bool ok = warp_refit_from_normal(ata, c1x, c1y, s1, c2x, c2y, s2, sh, Fn);
+                    if (lane == 0 && ok) {
+                        for (int i = 0; i < 9; ++i) sh.res[i] = Fn[i];
+                        sh.flag = 1;
                     }
                 }
                 __syncthreads();
@@ -448,7 +510,7 @@ int launch_ransac_verify(int32_t n_pairs, const int64_t* d_off, const int32_t* d
                              uint8_t* d_mask, float* d_sym, sfm_pair_metrics* d_metrics,
                              int32_t* d_status, cudaStream_t st, int64_t* launches) {
     if (n_pairs <= 0) return 0;
-    const int grid = n_pairs < 148 * 4 ? n_pairs : 148 * 4;
+    const int grid = n_pairs;   // one CTA per pair: the hardware scheduler balances the ragged pair costs
     ransac_verify_kernel<<<grid, kThreads, 0, st>>>(
         n_pairs, reinterpret_cast<const long long*>(d_off), d_cnt, d_pair_ids, d_pts1, d_pts2, d_F_in,
         prm, d_F, d_mask, d_sym, d_metrics, d_status);

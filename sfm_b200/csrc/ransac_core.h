@@ -251,6 +251,24 @@ SFM_HD T symmetric_dist(const T (&F)[9], T x1, T y1, T x2, T y2) {
     return T(0.5) * r * (T(1) / sqrt(n1) + T(1) / sqrt(n2));
 }
 
+#ifdef __CUDA_ARCH__
+// Hypothesis scoring form (device, float): two MUFU.RSQ instead of two sqrt + two divisions;
+// the hot loop of the RANSAC rounds (hypotheses x matches evaluations).
+template <>
+__device__ __forceinline__ float symmetric_dist<float>(const float (&F)[9], float x1, float y1, float x2,
+                                                       float y2) {
+    const float l2x = fmaf(F[0], x1, fmaf(F[1], y1, F[2]));
+    const float l2y = fmaf(F[3], x1, fmaf(F[4], y1, F[5]));
+    const float l2z = fmaf(F[6], x1, fmaf(F[7], y1, F[8]));
+    const float l1x = fmaf(F[0], x2, fmaf(F[3], y2, F[6]));
+    const float l1y = fmaf(F[1], x2, fmaf(F[4], y2, F[7]));
+    const float r = fabsf(fmaf(x2, l2x, fmaf(y2, l2y, l2z)));
+    const float n1 = fmaf(l1x, l1x, l1y * l1y), n2 = fmaf(l2x, l2x, l2y * l2y);
+    const float d = 0.5f * r * (rsqrtf(n1) + rsqrtf(n2));
+    return (n1 > 0.f && n2 > 0.f) ? d : 1e15f;
+}
+#endif
+
 // Residual used for inlier decisions: squared, compared against thr^2.
 template <typename T>
 SFM_HD T residual_sq(const T (&F)[9], T x1, T y1, T x2, T y2, bool symmetric) {
