@@ -134,6 +134,18 @@ class PairEngine:
                     F=v["F"], pack_off=pack_off, dense=dense)
 
     # ------------------------------------------------------------- host path
+    def _to_host(self, tensors: dict) -> dict:
+        """Device tensors -> numpy arrays backed by pinned host memory (torch's caching host
+        allocator recycles the blocks): every copy is queued asynchronously, one synchronisation."""
+        torch = self.torch
+        host = {}
+        for k, t in tensors.items():
+            h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            h.copy_(t, non_blocking=True)
+            host[k] = h
+        torch.cuda.current_stream(self.device).synchronize()
+        return {k: h.numpy() for k, h in host.items()}
+
     def match_pairs(self, pairs, only_ok: bool = True) -> PairBatchResult:
         """Public call: pair list in, host-side verified matches out (chunked)."""
         torch = self.torch
@@ -141,21 +153,23 @@ class PairEngine:
         parts = []
         for lo, hi in self._chunks(pairs):
             d = self._match_chunk(pairs[lo:hi], only_ok)
-            total = int(d["pack_off"][-1].item())          # one sync per chunk
+            # device -> pinned host, asynchronously; two synchronisations per chunk (the dense
+            # arrays' length is only known once pack_off has arrived)
+            small = self._to_host(dict(status=d["status"], count=d["count"], metrics=d["metrics"], F=d["F"],
+                                       pack_off=d["pack_off"]))
+            total = int(small["pack_off"][-1])
+            dn = d["dense"]
+            dense = self._to_host({k: dn[k][:total] for k in ("mq", "mt", "md2", "mask", "sym", "pts1", "pts2")})
             nt_small = self.counts[pairs[lo:hi, 1]] < 2
             nq_zero = self.counts[pairs[lo:hi, 0]] < 1
-            status = d["status"].cpu().numpy()
             # reference gate :268 and the Nt<2 failure of the ratio loop (:151)
-            status = np.where(nt_small | nq_zero, L.PAIR_TOO_FEW_FEATURES, status).astype(np.int32)
-            dn = d["dense"]
+            status = np.where(nt_small | nq_zero, L.PAIR_TOO_FEW_FEATURES, small["status"]).astype(np.int32)
             parts.append(dict(
-                pairs=pairs[lo:hi], status=status, count=d["count"].cpu().numpy(),
-                metrics=L.metrics_to_numpy(d["metrics"]), F=d["F"].cpu().numpy().reshape(-1, 3, 3),
-                pack_off=d["pack_off"].cpu().numpy(),
-                query_idx=dn["mq"][:total].cpu().numpy(), train_idx=dn["mt"][:total].cpu().numpy(),
-                sq_dist=dn["md2"][:total].cpu().numpy(), inlier_mask=dn["mask"][:total].cpu().numpy().astype(bool),
-                sym_err=dn["sym"][:total].cpu().numpy(), pts1=dn["pts1"][:total].cpu().numpy(),
-                pts2=dn["pts2"][:total].cpu().numpy()))
+                pairs=pairs[lo:hi], status=status, count=small["count"],
+                metrics=L.metrics_to_numpy(small["metrics"]), F=small["F"].reshape(-1, 3, 3),
+                pack_off=small["pack_off"], query_idx=dense["mq"], train_idx=dense["mt"], sq_dist=dense["md2"],
+                inlier_mask=dense["mask"].view(np.bool_), sym_err=dense["sym"], pts1=dense["pts1"],
+                pts2=dense["pts2"]))
         return _concat(parts, pairs)
 
 
@@ -167,6 +181,11 @@ def _concat(parts, pairs) -> PairBatchResult:
                                train_idx=z, sq_dist=z, inlier_mask=np.zeros(0, bool),
                                sym_err=np.zeros(0, np.float32), pts1=np.zeros((0, 2), np.float32),
                                pts2=np.zeros((0, 2), np.float32))
+    if len(parts) == 1:
+        q = parts[0]
+        return PairBatchResult(pairs=pairs, **{k: q[k] for k in (
+            "status", "count", "metrics", "F", "pack_off", "query_idx", "train_idx", "sq_dist", "inlier_mask",
+            "sym_err", "pts1", "pts2")})
     offs, base = [np.zeros(1, np.int64)], 0
     for q in parts:
         offs.append(q["pack_off"][1:] + base)

@@ -384,5 +384,6 @@ class Context:
 
 
 def metrics_to_numpy(t) -> np.ndarray:
-    """uint8 [P, 32] device tensor -> structured array (METRICS_DTYPE)."""
-    return t.cpu().numpy().view(METRICS_DTYPE).reshape(-1)
+    """uint8 [P, 32] device tensor (or its host copy as numpy) -> structured array (METRICS_DTYPE)."""
+    a = t if isinstance(t, np.ndarray) else t.cpu().numpy()
+    return a.view(METRICS_DTYPE).reshape(-1)
