@@ -147,7 +147,9 @@ __device__ __forceinline__ void top2k_insert_ordered(Top2K& s, int key, int col)
 // 16 folded accumulators of one row = one unit, chunk c of its tile; ut = uidrev << 1 of chunk 0.
 // MASKED: columns >= t_cnt (last, partial train tile) count as v = 0 (real accumulators are >= 0;
 // resolve_units skips them by column).  TREE_ONLY: timing probe.
-template <bool MASKED, bool TREE_ONLY>
+// SH0: train images up to 8192 rows (ubits = 8, no truncation): the key is m * 512 + ... with
+// compile-time constants.
+template <bool MASKED, bool TREE_ONLY, bool SH0>
 __device__ __forceinline__ void fold_chunk(Trk& s, const uint32_t (&acc)[16], int col0, int t_cnt,
                                            uint32_t slots, const KeyFmt& kf, uint32_t ut, uint32_t c) {
     int v[16];
@@ -165,7 +167,8 @@ __device__ __forceinline__ void fold_chunk(Trk& s, const uint32_t (&acc)[16], in
         return;
     }
     const uint32_t sb = s.k2 & 1u;
-    const uint32_t key = (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + ut + (sb - 2u * c);
+    const uint32_t key = SH0 ? (static_cast<uint32_t>(m) * 512u - 2u * c) + (ut + sb)
+                             : (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + ut + (sb - 2u * c);
     if (key > s.k2) {
         const uint32_t dst = slots + sb * kSlotStride;
 #pragma unroll
@@ -433,7 +436,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             const int32_t* nbase = norms_pad + t_pad;
             KeyFmt kf;
             kf.n_units = n_tiles * (kColsPerThread / kUnit);
-            kf.ubits = 32 - __clz(kf.n_units - 1);
+            kf.ubits = max(32 - __clz(kf.n_units - 1), 8);
             kf.sh = kf.ubits > 8 ? kf.ubits - 8 : 0;   // m < 2^23: (23 - sh) + ubits + 1 <= 32 bits
             kf.mul = 2u << kf.ubits;
             // units this thread will see: 8 per full tile, fewer in the last, partial one
@@ -455,7 +458,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 uint32_t v[2][16];
                 tmem_ld_32x16(taddr, v[0]);
                 const uint32_t ut = static_cast<uint32_t>(kf.n_units - 1 - t * (kColsPerThread / kUnit)) << 1;
-                if ((t + 1) * kTileN <= t_cnt) {
+                if ((t + 1) * kTileN <= t_cnt && kf.sh == 0) {
 #pragma unroll
                     for (int c = 0; c < kColsPerThread / 16; ++c) {
                         tmem_ld_wait();
@@ -467,7 +470,22 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                             __syncwarp();
                             if (lane == 0) mbar_arrive(empty);
                         }
-                        fold_chunk<false, MODE == 1>(sk, v[c & 1], t * kTileN + colbase + c * 16, t_cnt, my_slots,
+                        fold_chunk<false, MODE == 1, true>(sk, v[c & 1], t * kTileN + colbase + c * 16, t_cnt, my_slots,
+                                                     kf, ut, c);
+                    }
+                } else if ((t + 1) * kTileN <= t_cnt) {
+#pragma unroll
+                    for (int c = 0; c < kColsPerThread / 16; ++c) {
+                        tmem_ld_wait();
+                        if (c + 1 < kColsPerThread / 16) {
+                            tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
+                        } else {
+                            // every column of this thread is in registers: hand the accumulator back
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(empty);
+                        }
+                        fold_chunk<false, MODE == 1, false>(sk, v[c & 1], t * kTileN + colbase + c * 16, t_cnt, my_slots,
                                                      kf, ut, c);
                     }
                 } else {   // last, partial train tile: chunks wholly beyond the image are skipped
@@ -482,7 +500,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                             __syncwarp();
                             if (lane == 0) mbar_arrive(empty);
                         }
-                        if (col0 < t_cnt) fold_chunk<true, MODE == 1>(sk, v[c & 1], col0, t_cnt, my_slots, kf, ut, c);
+                        if (col0 < t_cnt) fold_chunk<true, MODE == 1, false>(sk, v[c & 1], col0, t_cnt, my_slots, kf, ut, c);
                     }
                 }
             }
