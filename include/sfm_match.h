@@ -228,8 +228,10 @@ SFM_API int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode);
 /* mbarrier suspend-time hints (ns; 0 = spin) of the kNN kernel's producer/MMA warps and of
  * its epilogue warps.  Tuning knob; results do not depend on it. */
 SFM_API int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_wait_ns);
-/* Timing-probe switches of the kNN kernel (results become meaningless): bit 0 the producer
- * skips the train-tile TMA loads, bit 1 the MMA warp skips the tcgen05.mma issue. */
+/* Probe switches of the kNN kernel.  Timing probes (results become meaningless): bit 0 the
+ * producer skips the train-tile TMA loads (N = 128 kernel), bit 1 the MMA warp skips the tcgen05.mma
+ * issue, bit 2 the wide kernel runs without its fix-up pass.  Test switch (results stay exact):
+ * bit 3 shrinks the wide kernel's fix-up list to 4 entries, so its overflow scan is exercised. */
 SFM_API int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags);
 /* Reads (synchronising `stream`) whether the registered set exceeded the fold range. */
 SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);

@@ -58,6 +58,8 @@ struct sfm_ctx {
     CUtensorMap tmap, tmap_x;
     CUtensorMap tmap_x32, tmap_ax32;   // wide kNN variant: fold operands as 32-byte rows (knn_wide.cu)
     DevBuf<uint8_t> d_bias32;
+    DevBuf<int32_t> d_fix_list;  // (work item, row) of the rows the wide kNN kernel leaves to its fix-up pass
+    static constexpr int32_t kFixCap = 1 << 18;
     bool have_tmap = false;
     DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
@@ -210,6 +212,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_flags.release();
     ctx->d_bias.release();
     ctx->d_bias32.release();
+    ctx->d_fix_list.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
     ctx->d_work.release();
@@ -263,6 +266,7 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     SFM_CUDA(ctx, ctx->d_flags.reserve(4));
     SFM_CUDA(ctx, ctx->d_bias.reserve(static_cast<size_t>(x_rows) * SFM_DESC_DIM));
     SFM_CUDA(ctx, ctx->d_bias32.reserve(static_cast<size_t>(total + SFM_TTILE) * 32));
+    SFM_CUDA(ctx, ctx->d_fix_list.reserve(2 * static_cast<size_t>(sfm_ctx::kFixCap)));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_x_off.p, ctx->h_x.data(), sizeof(int64_t) * (n_images + 1),
                                   cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
@@ -343,7 +347,9 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     if (km >= 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
-                                  ctx->knn_tuning.probe_flags, d_knn, ctx->num_sms, st, &ctx->launches);
+                                  ctx->knn_tuning.probe_flags, ctx->d_fix_list.p,
+                                  (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap, d_knn,
+                                  ctx->num_sms, st, &ctx->launches);
     if (!r && km <= 5 && !(km == 5 && ctx->knn_mode != 0))
         r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                              ctx->d_norms_pad.p, ctx->d_flags.p, km == 5 ? 9 : km, ctx->knn_tuning, d_knn,
@@ -601,7 +607,7 @@ int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
 
 int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags) {
     if (!ctx) return 1;
-    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 7u;
+    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 15u;
     return 0;
 }
 

@@ -290,7 +290,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
                  const __grid_constant__ CUtensorMap tmap_ax, const uint8_t* __restrict__ desc,
                  const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms, const int32_t* __restrict__ norms_pad,
-                 int32_t* __restrict__ flags, int force, uint32_t probe_flags, int4* __restrict__ out) {
+                 int32_t* __restrict__ flags, int force, uint32_t probe_flags, int2* __restrict__ fix_list,
+                 int fix_cap, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     // flags[0] != 0: some row's norm is beyond the fold range -> the generic kernel runs instead
@@ -546,8 +547,11 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     mrg.k2 = theirs ? b.k2 : r.k1;
                     mrg.i2 = theirs ? b.i2 : r.i1;
                 }
-                const unsigned fl = __ballot_sync(0xffffffffu, valid && flagged);
-                if (fl && lane == 0) atomicAdd(flags + 1, __popc(fl));   // rows left to knn_fix_kernel
+                if (valid && flagged) {   // rare: left to knn_fix_kernel
+                    atomicAdd(flags + 1, 1);   // statistics since sfm_set_images
+                    const int e = atomicAdd(flags + 2, 1);
+                    if (e < fix_cap) fix_list[e] = make_int2(static_cast<int>(w), row);
+                }
                 if (valid) {
                     const int i1 = mrg.i1 == INT_MAX ? -1 : mrg.i1;
                     const int i2 = mrg.i2 == INT_MAX ? -1 : mrg.i2;
@@ -602,90 +606,107 @@ __global__ void bias32_kernel(const int32_t* __restrict__ norms, long long total
     dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
 }
 
-// Rows the wide kernel flagged (out[row].x == kFlagged: two dropped units tie with the second kept
-// one) are recomputed here exactly on the CUDA cores.  One block per work item; its flagged rows
-// are taken one at a time by the whole block: threads stride over the train columns (ascending per
-// thread, strict compares), partial top-2s merged under the (key desc, index asc) order = OpenCV's
-// lowest-index tie rule.  flags[1] counts flagged rows since sfm_set_images; while it is 0 every
-// block exits at once.
-__global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __restrict__ work,
-                                                             const uint8_t* __restrict__ desc,
-                                                             const int32_t* __restrict__ norms,
-                                                             const int32_t* __restrict__ flags,
-                                                             int4* __restrict__ out) {
-    if (*(static_cast<volatile const int32_t*>(flags) + 1) == 0) return;
-    __shared__ int s_list[SFM_QBLOCK];
-    __shared__ int s_n;
-    __shared__ Top2K s_part[SFM_QBLOCK / 32];
-    const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + blockIdx.x));
-    const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + blockIdx.x) + 1);
-    const int q_row = w0.x, q_cnt = w0.y, t_row = w0.z, t_cnt = w0.w;
+// Rows the wide kernel flagged (two dropped units tie with the second kept one) are recomputed
+// here exactly on the CUDA cores.  The main kernel marks them (out[row].x == kFlagged) and appends
+// (work item, row) to a list -- flags[2] entries, at most fix_cap stored.  A block takes a row at a
+// time: threads stride over the train columns (ascending per thread, strict compares), partial
+// top-2s merged under the (key desc, index asc) order = OpenCV's lowest-index tie rule.  Rows
+// beyond the list capacity (degenerate data: everything ties) are found by scanning the work items.
+__device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, const uint8_t* __restrict__ desc,
+                        const int32_t* __restrict__ norms, int4* __restrict__ out, Top2K* s_part) {
+    const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
+    const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
+    const int q_row = w0.x, t_row = w0.z, t_cnt = w0.w;
     const long long out_row =
         static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_n = 0;
-    __syncthreads();
-    if (static_cast<int>(threadIdx.x) < q_cnt && out[out_row + threadIdx.x].x == kFlagged)
-        s_list[atomicAdd(&s_n, 1)] = threadIdx.x;
-    __syncthreads();
-    const int n = s_n;
-    for (int k = 0; k < n; ++k) {
-        const int r = s_list[k];
-        uint4 a[8];
+    uint4 a[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-            a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_row + r) * kRowBytes) + i);
-        Top2K best{INT_MIN, INT_MIN, INT_MAX, INT_MAX};
+    for (int i = 0; i < 8; ++i)
+        a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_row + r) * kRowBytes) + i);
+    Top2K best{INT_MIN, INT_MIN, INT_MAX, INT_MAX};
 #pragma unroll 2
-        for (int c = threadIdx.x; c < t_cnt; c += SFM_QBLOCK) {
-            const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes);
-            uint32_t dot = 0;
+    for (int c = threadIdx.x; c < t_cnt; c += SFM_QBLOCK) {
+        const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes);
+        uint32_t dot = 0;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint4 b = __ldg(bp + i);
-                dot = __dp4a(a[i].x, b.x, dot);
-                dot = __dp4a(a[i].y, b.y, dot);
-                dot = __dp4a(a[i].z, b.z, dot);
-                dot = __dp4a(a[i].w, b.w, dot);
-            }
-            top2k_insert(best, 2 * static_cast<int>(dot) - __ldg(norms + t_row + c), c);
+        for (int i = 0; i < 8; ++i) {
+            const uint4 b = __ldg(bp + i);
+            dot = __dp4a(a[i].x, b.x, dot);
+            dot = __dp4a(a[i].y, b.y, dot);
+            dot = __dp4a(a[i].z, b.z, dot);
+            dot = __dp4a(a[i].w, b.w, dot);
         }
-        auto merge = [](const Top2K& x, const Top2K& y) {
-            Top2K m;
-            if (key_before(x.k1, x.i1, y.k1, y.i1)) {
-                m.k1 = x.k1;
-                m.i1 = x.i1;
-                const bool keep = key_before(x.k2, x.i2, y.k1, y.i1);
-                m.k2 = keep ? x.k2 : y.k1;
-                m.i2 = keep ? x.i2 : y.i1;
-            } else {
-                m.k1 = y.k1;
-                m.i1 = y.i1;
-                const bool keep = key_before(y.k2, y.i2, x.k1, x.i1);
-                m.k2 = keep ? y.k2 : x.k1;
-                m.i2 = keep ? y.i2 : x.i1;
-            }
-            return m;
-        };
+        top2k_insert(best, 2 * static_cast<int>(dot) - __ldg(norms + t_row + c), c);
+    }
+    auto merge = [](const Top2K& x, const Top2K& y) {
+        Top2K m;
+        if (key_before(x.k1, x.i1, y.k1, y.i1)) {
+            m.k1 = x.k1;
+            m.i1 = x.i1;
+            const bool keep = key_before(x.k2, x.i2, y.k1, y.i1);
+            m.k2 = keep ? x.k2 : y.k1;
+            m.i2 = keep ? x.i2 : y.i1;
+        } else {
+            m.k1 = y.k1;
+            m.i1 = y.i1;
+            const bool keep = key_before(y.k2, y.i2, x.k1, x.i1);
+            m.k2 = keep ? y.k2 : x.k1;
+            m.i2 = keep ? y.i2 : x.i1;
+        }
+        return m;
+    };
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            Top2K b;
-            b.k1 = __shfl_xor_sync(0xffffffffu, best.k1, o);
-            b.k2 = __shfl_xor_sync(0xffffffffu, best.k2, o);
-            b.i1 = __shfl_xor_sync(0xffffffffu, best.i1, o);
-            b.i2 = __shfl_xor_sync(0xffffffffu, best.i2, o);
-            best = merge(best, b);
-        }
-        if (lane == 0) s_part[warp] = best;
+    for (int o = 16; o > 0; o >>= 1) {
+        Top2K b;
+        b.k1 = __shfl_xor_sync(0xffffffffu, best.k1, o);
+        b.k2 = __shfl_xor_sync(0xffffffffu, best.k2, o);
+        b.i1 = __shfl_xor_sync(0xffffffffu, best.i1, o);
+        b.i2 = __shfl_xor_sync(0xffffffffu, best.i2, o);
+        best = merge(best, b);
+    }
+    if (lane == 0) s_part[warp] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        Top2K m = s_part[0];
+        for (int k = 1; k < SFM_QBLOCK / 32; ++k) m = merge(m, s_part[k]);
+        const int na = __ldg(norms + q_row + r);
+        const int i1 = m.i1 == INT_MAX ? -1 : m.i1;
+        const int i2 = m.i2 == INT_MAX ? -1 : m.i2;
+        out[out_row + r] = make_int4(i1, i2, i1 < 0 ? INT_MAX : na - m.k1, i2 < 0 ? INT_MAX : na - m.k2);
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __restrict__ work, long long n_work,
+                                                             const uint8_t* __restrict__ desc,
+                                                             const int32_t* __restrict__ norms,
+                                                             const int32_t* __restrict__ flags,
+                                                             const int2* __restrict__ fix_list, int fix_cap,
+                                                             int4* __restrict__ out) {
+    const int cnt = *(static_cast<volatile const int32_t*>(flags) + 2);
+    if (cnt == 0) return;
+    __shared__ Top2K s_part[SFM_QBLOCK / 32];
+    __shared__ int s_list[SFM_QBLOCK];
+    __shared__ int s_n;
+    const int n_list = cnt < fix_cap ? cnt : fix_cap;
+    for (int e = blockIdx.x; e < n_list; e += gridDim.x) {
+        const int2 it = __ldg(fix_list + e);
+        fix_row(work, it.x, it.y, desc, norms, out, s_part);
+    }
+    if (cnt <= fix_cap) return;
+    for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {   // list overflow: scan for the markers
+        const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
+        const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
+        const long long out_row =
+            static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
+        if (threadIdx.x == 0) s_n = 0;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            Top2K m = s_part[0];
-            for (int w = 1; w < SFM_QBLOCK / 32; ++w) m = merge(m, s_part[w]);
-            const int na = __ldg(norms + q_row + r);
-            const int i1 = m.i1 == INT_MAX ? -1 : m.i1;
-            const int i2 = m.i2 == INT_MAX ? -1 : m.i2;
-            out[out_row + r] = make_int4(i1, i2, i1 < 0 ? INT_MAX : na - m.k1, i2 < 0 ? INT_MAX : na - m.k2);
-        }
+        if (static_cast<int>(threadIdx.x) < w0.y && out[out_row + threadIdx.x].x == kFlagged)
+            s_list[atomicAdd(&s_n, 1)] = threadIdx.x;
+        __syncthreads();
+        const int n = s_n;
+        for (int k = 0; k < n; ++k) fix_row(work, w, s_list[k], desc, norms, out, s_part);
         __syncthreads();
     }
 }
@@ -757,7 +778,7 @@ template <int MODE>
 cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                            const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                            const int32_t* d_norms_pad, int32_t* d_flags, int force, uint32_t probe_flags,
-                           int32_t* d_knn, unsigned grid, cudaStream_t st) {
+                           int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(knn2_wide_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -766,8 +787,8 @@ cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, c
         configured = true;
     }
     knn2_wide_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms,
-                                                              d_norms_pad, d_flags, force, probe_flags,
-                                                              reinterpret_cast<int4*>(d_knn));
+                                                              d_norms_pad, d_flags, force, probe_flags, d_fix_list,
+                                                              fix_cap, reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
 }
 
@@ -785,24 +806,26 @@ void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                      const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                      const int32_t* d_norms_pad,
-                     int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_knn, int num_sms,
-                     cudaStream_t st, int64_t* launches) {
+                     int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_fix_list,
+                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches) {
     if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
-    cudaError_t e;
+    int2* fl = reinterpret_cast<int2*>(d_fix_list);
+    cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, sizeof(int32_t), st);   // length of this launch's fix list
+    if (e != cudaSuccess) return static_cast<int>(e);
     if (variant == 1)
         e = launch_variant<1>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
-                              d_knn, grid, st);
+                              fl, fix_cap, d_knn, grid, st);
     else if (variant == 2)
         e = launch_variant<2>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
-                              d_knn, grid, st);
+                              fl, fix_cap, d_knn, grid, st);
     else
         e = launch_variant<0>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, force,
-                              probe_flags, d_knn, grid, st);
+                              probe_flags, fl, fix_cap, d_knn, grid, st);
     ++*launches;
     if (e == cudaSuccess && variant == 0 && !(probe_flags & 4u)) {   // (probe bit 2: main kernel alone)
-        knn_fix_kernel<<<static_cast<unsigned>(n_work), SFM_QBLOCK, 0, st>>>(d_work, d_desc, d_norms, d_flags,
-                                                                            reinterpret_cast<int4*>(d_knn));
+        knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_flags, fl, fix_cap,
+                                                          reinterpret_cast<int4*>(d_knn));
         ++*launches;
         e = cudaGetLastError();
     }

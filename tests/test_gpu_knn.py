@@ -201,6 +201,29 @@ def test_wide_fold_tile_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
+def test_knn_wide_fixup_paths(ctx):
+    """Data made of few distinct descriptors: unit maxima tie everywhere, so the wide kernel's
+    tied-unit recompute and its brute-force fix-up pass (list driven, and the overflow scan with the
+    list shrunk to 4 entries) produce the rows; all must equal the oracle incl. the tie rule."""
+    rng = np.random.default_rng(77)
+    base = _sift_like([6], 41)[0]
+    descs = [base[rng.integers(0, 6, n)] for n in (300, 1100, 520)]
+    register(ctx, descs)
+    pairs = [(0, 1), (1, 2), (2, 0), (1, 0)]
+    for pf in (0, 8):
+        ctx.set_knn_mode(5)
+        ctx.set_knn_probe_flags(pf)
+        try:
+            before = ctx.brute_rows()
+            got, ro = gpu_knn(ctx, pairs)
+            assert ctx.brute_rows() > before          # the fix-up pass really ran
+        finally:
+            ctx.set_knn_mode(0)
+            ctx.set_knn_probe_flags(0)
+        for p, (i, j) in enumerate(pairs):
+            check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
+
+
 def test_knn_wide_long_train_images(ctx):
     """Wide kernel with train images beyond 8192 rows: unit ids need more than 8 key bits, the unit
     maxima are truncated in the packed keys and ties on the truncated value are recomputed."""
