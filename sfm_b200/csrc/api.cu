@@ -347,7 +347,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     if (km >= 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
-                                  ctx->knn_tuning.probe_flags, ctx->d_fix_list.p,
+                                  ctx->knn_tuning, ctx->d_fix_list.p,
                                   (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap, d_knn,
                                   ctx->num_sms, st, &ctx->launches);
     if (!r && km <= 5 && !(km == 5 && ctx->knn_mode != 0))

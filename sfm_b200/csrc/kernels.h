@@ -50,7 +50,7 @@ void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                      const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                      const int32_t* d_norms_pad,
-                     int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_fix_list,
+                     int32_t* d_flags, int variant, int force, const struct KnnTuning& tn, int32_t* d_fix_list,
                      int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                       int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches);

@@ -290,8 +290,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
                  const __grid_constant__ CUtensorMap tmap_ax, const uint8_t* __restrict__ desc,
                  const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms, const int32_t* __restrict__ norms_pad,
-                 int32_t* __restrict__ flags, int force, uint32_t probe_flags, int2* __restrict__ fix_list,
-                 int fix_cap, int4* __restrict__ out) {
+                 int32_t* __restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns,
+                 uint32_t epi_wait_ns, int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     // flags[0] != 0: some row's norm is beyond the fold range -> the generic kernel runs instead
@@ -354,7 +354,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             ap.advance();
             const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait(&sm.b_empty[bp.stage], bp.phase ^ 1);
+                mbar_wait_suspend(&sm.b_empty[bp.stage], bp.phase ^ 1, wait_ns);
                 if (elect_one()) {
                     uint8_t* dst = sm.b + size_t(bp.stage) * kStageBytes;
                     // rows beyond the train image are masked in the epilogue: a second half that
@@ -382,13 +382,13 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             mbar_wait(&sm.a_full[ap.stage], ap.phase);
             const uint64_t adesc0 = make_kmajor_sw128_desc(smem_u32(sm.a + size_t(ap.stage) * kABlockBytes));
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait(&sm.b_full[bp.stage], bp.phase);
+                mbar_wait_suspend(&sm.b_full[bp.stage], bp.phase, wait_ns);
                 const uint32_t bsm = smem_u32(sm.b + size_t(bp.stage) * kStageBytes);
                 const uint64_t bdesc0 = make_kmajor_sw128_desc(bsm);
                 const uint64_t xdesc = make_kmajor_sw32_desc(bsm + kBTileBytes);
 #pragma unroll
                 for (int a = 0; a < kATiles; ++a) {
-                    mbar_wait(&sm.t_empty[a], tphase ^ 1);
+                    mbar_wait_suspend(&sm.t_empty[a], tphase ^ 1, wait_ns);
                     tc_fence_after();
                     const uint32_t d = tmem_base + a * kTileN;
                     const uint64_t adesc = adesc0 + uint64_t(a) * (kATileBytes >> 4);
@@ -446,7 +446,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                                min(max((rem + kUnit - 1) / kUnit, 0), kColsPerThread / kUnit);
             Trk sk{1, 0, 0, 0};   // empty keys: k1 owns slot 1, k2 slot 0 (the first unit is parked in slot 0)
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait(full, tphase);
+                mbar_wait_suspend(full, tphase, epi_wait_ns);
                 tc_fence_after();
                 tphase ^= 1;
                 if (MODE == 2) {   // timing probe: TMA + MMA pipeline alone
@@ -777,7 +777,7 @@ debug_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
 template <int MODE>
 cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                            const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
-                           const int32_t* d_norms_pad, int32_t* d_flags, int force, uint32_t probe_flags,
+                           const int32_t* d_norms_pad, int32_t* d_flags, int force, const KnnTuning& tn,
                            int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
@@ -787,8 +787,8 @@ cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, c
         configured = true;
     }
     knn2_wide_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms,
-                                                              d_norms_pad, d_flags, force, probe_flags, d_fix_list,
-                                                              fix_cap, reinterpret_cast<int4*>(d_knn));
+                                                              d_norms_pad, d_flags, force, tn.probe_flags, tn.wait_ns,
+                                                              tn.epi_wait_ns, d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
 }
 
@@ -806,7 +806,7 @@ void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                      const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                      const int32_t* d_norms_pad,
-                     int32_t* d_flags, int variant, int force, uint32_t probe_flags, int32_t* d_fix_list,
+                     int32_t* d_flags, int variant, int force, const KnnTuning& tn, int32_t* d_fix_list,
                      int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches) {
     if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
@@ -814,16 +814,16 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
     cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, sizeof(int32_t), st);   // length of this launch's fix list
     if (e != cudaSuccess) return static_cast<int>(e);
     if (variant == 1)
-        e = launch_variant<1>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
+        e = launch_variant<1>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, tn,
                               fl, fix_cap, d_knn, grid, st);
     else if (variant == 2)
-        e = launch_variant<2>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, probe_flags,
+        e = launch_variant<2>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1, tn,
                               fl, fix_cap, d_knn, grid, st);
     else
         e = launch_variant<0>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, force,
-                              probe_flags, fl, fix_cap, d_knn, grid, st);
+                              tn, fl, fix_cap, d_knn, grid, st);
     ++*launches;
-    if (e == cudaSuccess && variant == 0 && !(probe_flags & 4u)) {   // (probe bit 2: main kernel alone)
+    if (e == cudaSuccess && variant == 0 && !(tn.probe_flags & 4u)) {   // (probe bit 2: main kernel alone)
         knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_flags, fl, fix_cap,
                                                           reinterpret_cast<int4*>(d_knn));
         ++*launches;
