@@ -185,7 +185,7 @@ __device__ void write_skip(int p, int m, int status, double* F_out, sfm_pair_met
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32_t* __restrict__ cnt,
                      const int32_t* __restrict__ pair_ids, const float* __restrict__ pts1,
                      const float* __restrict__ pts2, const double* __restrict__ F_in,
