@@ -46,7 +46,8 @@ def _dmatch(q: int, t: int, d: float):
 class ImageMatcher:
     """utils/find_matches.py:10.  One instance per run, single-threaded caller."""
 
-    def __init__(self, data_dir, device: int = 0, mutual: bool = False, write_visualizations: bool = False):
+    def __init__(self, data_dir, device: int = 0, mutual: bool = False, write_visualizations: bool = False,
+                 writer_threads: int = 8):
         self.data_dir = Path(data_dir)
         self.image_dir = self.data_dir / "images"
         self.silhouette_dir = self.data_dir / "silhouettes"
@@ -60,6 +61,7 @@ class ImageMatcher:
         self.device = device
         self.mutual = mutual            # README.md:108 mutual-NN check; off = the reference's code path
         self.write_visualizations = write_visualizations
+        self.writer_threads = int(writer_threads)   # 0: write the pair files synchronously
         self._engine = None
         self.last_batch = None          # PairBatchResult of the last process_image_range
 
@@ -189,24 +191,41 @@ class ImageMatcher:
                  trainIdx=t.astype(np.int64), distance=dist.astype(np.float64), inlier_mask=inlier_mask)
 
     def _emit(self, res, names):
-        """Write the files of every passing pair of a PairBatchResult and build the CSV rows."""
-        rows = []
-        for p, (img1_path, img2_path, pair_name) in enumerate(names):
-            if res.status[p] != L.PAIR_OK:
-                continue
-            sl = res.pair_slice(p)
-            mask = res.inlier_mask[sl]
-            m = res.metrics[p]
-            self._save_pair_arrays(pair_name, res.pts1[sl], res.pts2[sl], res.F[p], mask,
-                                   res.query_idx[sl], res.train_idx[sl], res.distance(p))
-            n = int(m["total_matches"])
-            rows.append({
-                "pair_name": pair_name, "img1": Path(img1_path).name, "img2": Path(img2_path).name,
-                "num_matches": n, "num_inliers": np.int64(mask.sum()),
-                "inlier_ratio": np.float64(mask.sum()) / np.float64(n),               # np.mean(bool), :193
-                "reprojection_error": np.float32(m["reprojection_error"]),
-                "well_distributed": bool(m["well_distributed"]),
-            })
+        """Write the files of every passing pair of a PairBatchResult and build the CSV rows.
+        The four files per pair (:312-327) are written by a small thread pool (row N1 of SURVEY 8f:
+        at scale the writer, not the GPU, sets the pace; file I/O and zlib release the GIL); all
+        writes have finished when this returns, as in the reference."""
+        rows, jobs = [], []
+        pool = None
+        if self.writer_threads > 0:
+            from concurrent.futures import ThreadPoolExecutor
+            pool = ThreadPoolExecutor(max_workers=self.writer_threads)
+        try:
+            for p, (img1_path, img2_path, pair_name) in enumerate(names):
+                if res.status[p] != L.PAIR_OK:
+                    continue
+                sl = res.pair_slice(p)
+                mask = res.inlier_mask[sl]
+                m = res.metrics[p]
+                args = (pair_name, res.pts1[sl], res.pts2[sl], res.F[p], mask, res.query_idx[sl],
+                        res.train_idx[sl], res.distance(p))
+                if pool is None:
+                    self._save_pair_arrays(*args)
+                else:
+                    jobs.append(pool.submit(self._save_pair_arrays, *args))
+                n = int(m["total_matches"])
+                rows.append({
+                    "pair_name": pair_name, "img1": Path(img1_path).name, "img2": Path(img2_path).name,
+                    "num_matches": n, "num_inliers": np.int64(mask.sum()),
+                    "inlier_ratio": np.float64(mask.sum()) / np.float64(n),               # np.mean(bool), :193
+                    "reprojection_error": np.float32(m["reprojection_error"]),
+                    "well_distributed": bool(m["well_distributed"]),
+                })
+            for j in jobs:
+                j.result()                          # re-raises a writer's exception
+        finally:
+            if pool is not None:
+                pool.shutdown(wait=True)
         return rows
 
     def collect_features(self, start_idx, end_idx, mask=False):

@@ -163,6 +163,38 @@ def test_knn_8k_config_sample_vs_oracle_and_properties(ctx):
             assert got[i, j, :, 2].min() == got[j, i, :, 2].min()
 
 
+def test_knn_32k_config_sample_vs_oracle_and_properties(ctx):
+    """BASELINE config 5 shape (32768-descriptor images, 128 train tiles per work item: 10-bit unit
+    ids, truncated maxima in the keys): sampled query rows against the oracle, then
+    size-independent properties over the full 32k x 32k pairs."""
+    from sfm_b200 import synth
+    n, nd = 3, 32768
+    s = synth.make_image_set(n, nd, seed=synth.BASE_SEED + 4, device="cuda", tie_frac=0.01)
+    ctx.set_images(s.desc, s.kps, s.offsets.numpy())
+    pairs = np.array([(i, j) for i in range(n) for j in range(n)], np.int32)
+    knn, ro = ctx.knn2(pairs)
+    knn2, _ = ctx.knn2(pairs)
+    torch.cuda.synchronize()
+    assert torch.equal(knn, knn2)                              # deterministic
+    got = knn.cpu().numpy().reshape(n, n, nd, 4)
+    descs = [s.image(i)[0].cpu().numpy() for i in range(n)]
+    rows = np.random.default_rng(5).choice(nd, 192, replace=False)
+    rows.sort()
+    for (i, j) in [(0, 1), (2, 0), (1, 1)]:
+        idx, sqd = oknn.knn2_l2_numpy(descs[i][rows], descs[j])
+        assert np.array_equal(got[i, j][rows, :2], idx), "neighbour indices differ"
+        assert np.array_equal(got[i, j][rows, 2:], sqd), "squared distances differ"
+    assert np.all(got[..., 2] <= got[..., 3])                  # ascending distances
+    assert np.all(got[..., 0] != got[..., 1])
+    assert np.all((got[..., :2] >= 0) & (got[..., :2] < nd))
+    for i in range(n):                                         # self match: distance 0, lowest index
+        assert np.all(got[i, i, :, 2] == 0)
+        assert np.all(got[i, i, :, 0] <= np.arange(nd))
+    for i in range(n):                                         # min over rows == min over columns
+        for j in range(i + 1, n):
+            assert got[i, j, :, 2].min() == got[j, i, :, 2].min()
+
+
 # ---------------------------------------------------------------- kernel variants
 FOLD_C = 255 * 31 * 255 + 254          # sfm_b200/csrc/knn.cu kFoldC
 def _sift_like(sizes, seed):
