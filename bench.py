@@ -275,22 +275,19 @@ def run_b200(args):
         else:
             o = off
         eng.set_images(d, k, o)
-        res = eng.match_pairs(my_pairs)                        # host-side results (D2H inside)
-        nbytes = sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
-                                                       "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1", "pts2"))
-        if world > 1:
-            local = dict(pairs=torch.from_numpy(res.pairs).to(dev), status=torch.from_numpy(res.status).to(dev),
-                         count=torch.from_numpy(res.count).to(dev),
-                         metrics=torch.from_numpy(res.metrics.view(np.uint8).reshape(len(res.status), -1)).to(dev),
-                         F=torch.from_numpy(res.F).to(dev),
-                         kept=torch.from_numpy(np.diff(res.pack_off)).to(dev),
-                         dense=dict(mq=torch.from_numpy(res.query_idx).to(dev), mt=torch.from_numpy(res.train_idx).to(dev),
-                                    md2=torch.from_numpy(res.sq_dist).to(dev),
-                                    mask=torch.from_numpy(res.inlier_mask.view(np.uint8)).to(dev),
-                                    pts1=torch.from_numpy(res.pts1).to(dev), pts2=torch.from_numpy(res.pts2).to(dev)))
-            g = D.gather_batch_results(local)                  # match lists gathered back to rank 0
-            if g is not None:
-                _ = g["status"].cpu(), g["dense"]["mq"].cpu()
+        if world == 1:
+            res = eng.match_pairs(my_pairs)                    # host-side results (D2H inside)
+            return sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
+                                                        "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1",
+                                                        "pts2"))
+        local = eng.match_pairs_device(my_pairs)               # results stay on the device ...
+        g = D.gather_batch_results(local)                      # ... match lists gathered back to rank 0 (NCCL)
+        nbytes = 0
+        if g is not None:                                      # rank 0 alone copies them to the host
+            flat = {k: g[k] for k in ("pairs", "status", "count", "metrics", "F", "pack_off")}
+            flat.update({"dense_" + k: v for k, v in g["dense"].items()})
+            host = eng._to_host(flat)
+            nbytes = sum(a.nbytes for a in host.values())
         return nbytes
 
     e2e_step()

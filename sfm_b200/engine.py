@@ -133,6 +133,31 @@ class PairEngine:
         return dict(pairs=pairs, row_off=ro, knn=knn, count=cnt, status=v["status"], metrics=v["metrics"],
                     F=v["F"], pack_off=pack_off, dense=dense)
 
+    def match_pairs_device(self, pairs, only_ok: bool = True) -> dict:
+        """Like match_pairs but the results stay on the device, in the layout
+        dist.gather_batch_results expects (per-pair tensors + 'kept' + dense arrays): the
+        multi-GPU path gathers them on rank 0 over NCCL before anything crosses PCIe."""
+        torch = self.torch
+        pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
+        parts = []
+        for lo, hi in self._chunks(pairs):
+            d = self._match_chunk(pairs[lo:hi], only_ok)
+            total = int(d["pack_off"][-1].item())          # one sync per chunk
+            bad = torch.from_numpy((self.counts[pairs[lo:hi, 1]] < 2) | (self.counts[pairs[lo:hi, 0]] < 1))
+            status = torch.where(bad.to(self.device), torch.full_like(d["status"], L.PAIR_TOO_FEW_FEATURES),
+                                 d["status"])
+            dn = d["dense"]
+            parts.append(dict(
+                pairs=torch.from_numpy(pairs[lo:hi]).to(self.device), status=status, count=d["count"].clone(),
+                metrics=d["metrics"].clone(), F=d["F"].clone(),
+                kept=(d["pack_off"][1:] - d["pack_off"][:-1]).to(torch.int32),
+                dense={k: dn[k][:total].clone() for k in ("mq", "mt", "md2", "mask", "sym", "pts1", "pts2")}))
+        if len(parts) == 1:
+            return parts[0]
+        out = {k: torch.cat([q[k] for q in parts]) for k in ("pairs", "status", "count", "metrics", "F", "kept")}
+        out["dense"] = {k: torch.cat([q["dense"][k] for q in parts]) for k in parts[0]["dense"]}
+        return out
+
     # ------------------------------------------------------------- host path
     def _to_host(self, tensors: dict) -> dict:
         """Device tensors -> numpy arrays backed by pinned host memory (torch's caching host
