@@ -96,7 +96,7 @@ __device__ __forceinline__ uint64_t make_kmajor_sw32_desc(uint32_t smem_addr) {
 // 16 accumulators are stored to shared-memory slot `slot`, the slot of the key it evicts (k2).
 // At the end of the work item the parked values give the exact top-2 (resolve_units).  A third
 // unit can only matter if its (truncated) maximum equals k2's: then dm names it and its 16 keys
-// are recomputed from the descriptors (recompute_unit, ~2 % of rows); if dd ties as well the row
+// are recomputed from the descriptors (recompute_units, ~2 % of rows); if dd ties as well the row
 // is flagged for knn_fix_kernel (brute force).  ubits / sh depend on the train image size:
 // 8192 rows need 8 bits and no truncation, 32768 rows 10 bits and sh = 2 (ties on the truncated
 // maximum are merely more frequent; the logic above is exact for any monotone truncation).
@@ -199,6 +199,9 @@ __device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const K
     const int c1 = n_seen >= 1 ? key_col(s.k1, kf, colbase) : -1;
     const int c2 = n_seen >= 2 ? key_col(s.k2, kf, colbase) : -1;
     const bool second_first = c2 >= 0 && c2 < c1;
+    // both neighbours of this thread's columns have v >= the second unit maximum (a lower bound of
+    // it when the key holds a truncated maximum): everything below is skipped without forming a key
+    const int vmin = n_seen >= 2 ? static_cast<int>((s.k2 >> (kf.ubits + 1)) << kf.sh) : 0;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         const bool take2 = (pass == 0) == second_first;
@@ -215,36 +218,48 @@ __device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const K
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int col = c + 4 * g + e;
-                if (col < t_cnt) top2k_insert(r, 2 * vv[e] - (pp[e] + 2 * kFoldC), col);
+                if (col < t_cnt && vv[e] >= vmin) top2k_insert(r, 2 * vv[e] - (pp[e] + 2 * kFoldC), col);
             }
         }
     }
     return r;
 }
 
-// Rare path: the exact keys of one dropped unit, recomputed from the descriptors on the CUDA
-// cores and merged under the (key desc, index asc) order.
-__device__ __noinline__ Top2K recompute_unit(Top2K r, const uint8_t* __restrict__ desc, int q_abs, int t_row,
-                                             int col, int t_cnt, const int32_t* __restrict__ nbase) {
-    uint4 a[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-        a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_abs) * kRowBytes) + i);
-#pragma unroll 1
-    for (int e = 0; e < kUnit; ++e) {
-        const int c = col + e;
-        if (c >= t_cnt) break;
-        const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes);
+// Rare path (2 % of rows): the exact keys of one dropped unit, recomputed from the descriptors on
+// the CUDA cores by the WHOLE warp for one row at a time -- lane e and lane 16 + e each take 64
+// bytes of train row col + e (dp4a), the 16 keys are then fed to the row's lane in column order
+// and merged under the (key desc, index asc) order.  All lanes must call it (uniform control flow).
+__device__ __noinline__ Top2K recompute_units(Top2K r, bool need, int q_abs, int col, const uint8_t* __restrict__ desc,
+                                              int t_row, int t_cnt, const int32_t* __restrict__ nbase) {
+    const int lane = threadIdx.x & 31;
+    unsigned todo = __ballot_sync(0xffffffffu, need);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int qa = __shfl_sync(0xffffffffu, q_abs, src);
+        const int cc = __shfl_sync(0xffffffffu, col, src);
+        const int c = cc + (lane & 15);
+        const int part = lane >> 4;   // which 64-byte half of the 128-byte rows
         uint32_t dot = 0;
+        if (c < t_cnt) {
+            const uint4* ap = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(qa) * kRowBytes) + 4 * part;
+            const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes) + 4 * part;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const uint4 b = __ldg(bp + i);
-            dot = __dp4a(a[i].x, b.x, dot);
-            dot = __dp4a(a[i].y, b.y, dot);
-            dot = __dp4a(a[i].z, b.z, dot);
-            dot = __dp4a(a[i].w, b.w, dot);
+            for (int i = 0; i < 4; ++i) {
+                const uint4 a = __ldg(ap + i), b = __ldg(bp + i);
+                dot = __dp4a(a.x, b.x, dot);
+                dot = __dp4a(a.y, b.y, dot);
+                dot = __dp4a(a.z, b.z, dot);
+                dot = __dp4a(a.w, b.w, dot);
+            }
         }
-        top2k_insert_ordered(r, 2 * static_cast<int>(dot) - __ldg(nbase + c), c);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 16);
+        const int key = c < t_cnt ? 2 * static_cast<int>(dot) - __ldg(nbase + c) : INT_MIN;
+#pragma unroll 1
+        for (int e = 0; e < kUnit; ++e) {
+            const int ke = __shfl_sync(0xffffffffu, key, e);
+            if (lane == src && cc + e < t_cnt) top2k_insert_ordered(r, ke, cc + e);
+        }
     }
     return r;
 }
@@ -513,8 +528,8 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             // a dropped unit whose (truncated) maximum equals the second kept one may hold a candidate:
             // the best dropped one is recomputed here, a second one sends the row to knn_fix_kernel
             const uint32_t mf = kf.ubits + 1;
-            if (valid && n_seen >= 3 && (sk.dm >> mf) == (sk.k2 >> mf))
-                r = recompute_unit(r, desc, q_row + row, t_row, key_col(sk.dm, kf, colbase), t_cnt, nbase);
+            r = recompute_units(r, valid && n_seen >= 3 && (sk.dm >> mf) == (sk.k2 >> mf), q_row + row,
+                                key_col(sk.dm, kf, colbase), desc, t_row, t_cnt, nbase);
             const bool tie = n_seen >= 4 && (sk.dd >> mf) == (sk.k2 >> mf);
             // the thread of the upper column half hands its top-2 to the lower half's thread,
             // which merges under the (key, lowest index) order and writes the row
