@@ -183,6 +183,32 @@ SFM_API int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row
                      int32_t* o_md2, uint8_t* o_mask, float* o_sym, float* o_pts1, float* o_pts2,
                      void* stream);
 
+/* ---- 2-D radius matching of track points ----------------- */
+/* The dense distance test inside StructureFromMotion.find_2d3d_matches
+ * (utils/sfm_reconstruction.py:211-213):
+ *     distances = np.linalg.norm(valid_track_points[:, None] - other_img_pts, axis=2)
+ *     matches = np.where(distances < MATCHING_THRESHOLD)
+ * for n_seg segments at once (one segment = the tracks that contain the other
+ * image x the points of one image pair, :181-207).
+ *   h_track_off i64 [n_seg+1]  track rows of segment s = [off[s], off[s+1])
+ *   d_tracks    f64 [rows,2]   valid_track_points of all segments
+ *   h_pt_off    i64 [n_seg+1]  point ranges
+ *   d_pts       f64 [n_pts,2]  other_img_pts (the f32 files widened exactly)
+ *   threshold                  MATCHING_THRESHOLD (:14); the test is the f64
+ *                              expression above, decision for decision
+ *   h_seg_off   i64 [n_seg+1]  (out) match ranges: segment s owns entries
+ *                              [h_seg_off[s], h_seg_off[s+1]); [n_seg] = total
+ *   d_out_track, d_out_pt  i32 [cap] (out) the two arrays np.where returns, per
+ *                              segment in its order (track-major, point ascending);
+ *                              indices are local to the segment
+ * Pass d_out_track = d_out_pt = NULL to size the result (h_seg_off only).
+ * If the total h_seg_off[n_seg] exceeds cap nothing is written to the output
+ * arrays (the call still returns 0): call again with room.  Synchronises `stream`. */
+SFM_API int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off,
+                     const double* d_tracks, const int64_t* h_pt_off, const double* d_pts,
+                     double threshold, int64_t* h_seg_off, int32_t* d_out_track,
+                     int32_t* d_out_pt, int64_t cap, void* stream);
+
 /* ---- measurement helpers ---------------------------------------------- */
 /* Number of kernel launches issued by this context since creation. */
 SFM_API int64_t sfm_launch_count(sfm_ctx* ctx);

@@ -74,6 +74,11 @@ struct sfm_ctx {
     DevBuf<sfm::WorkItem> d_work;
     std::vector<int64_t> h_meta;
 
+    // sfm_radius_match scratch
+    DevBuf<sfm::RadiusBlock> d_rblocks;
+    DevBuf<long long> d_rcnt, d_roff;
+    std::vector<sfm::RadiusBlock> h_rblocks;
+
     int fail(const char* fmt, ...) {
         char buf[512];
         va_list ap;
@@ -474,6 +479,86 @@ int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row_off, co
     sfm::launch_pack(n_pairs, ctx->d_meta.p + n1, d_count, d_status, only_ok ? 1 : 0, d_pack_off, a, st,
                      &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
+    return 0;
+}
+
+// Smallest s with sqrt_rn(s) >= thr: sqrt(s) < thr <=> s < radius_limit(thr) for every s >= 0
+// (sqrt_rn is monotone; positive doubles order like their bit patterns).
+static double radius_limit(double thr) {
+    if (!(thr > 0.0)) return 0.0;                       // sqrt(s) < thr never holds
+    if (std::isinf(thr)) return thr;
+    uint64_t lo = 0, hi = 0x7ff0000000000000ull;        // sqrt(+0) = 0 < thr, sqrt(inf) = inf >= thr
+    while (hi - lo > 1) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        double s;
+        std::memcpy(&s, &mid, sizeof(s));
+        if (std::sqrt(s) >= thr) hi = mid; else lo = mid;
+    }
+    double s;
+    std::memcpy(&s, &hi, sizeof(s));
+    return s;
+}
+
+int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, const double* d_tracks,
+                     const int64_t* h_pt_off, const double* d_pts, double threshold, int64_t* h_seg_off,
+                     int32_t* d_out_track, int32_t* d_out_pt, int64_t cap, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_seg < 0) return ctx->fail("n_seg < 0");
+    if (!h_seg_off) return ctx->fail("h_seg_off is NULL");
+    if (n_seg == 0) {
+        h_seg_off[0] = 0;
+        return 0;
+    }
+    if (!h_track_off || !h_pt_off) return ctx->fail("NULL offset array");
+    if ((d_out_track == nullptr) != (d_out_pt == nullptr)) return ctx->fail("pass both output arrays or neither");
+    if (std::isnan(threshold)) return ctx->fail("threshold is NaN");
+    auto& blocks = ctx->h_rblocks;
+    blocks.clear();
+    for (int32_t s = 0; s < n_seg; ++s) {
+        const int64_t nt = h_track_off[s + 1] - h_track_off[s], np = h_pt_off[s + 1] - h_pt_off[s];
+        if (nt < 0 || np < 0 || h_track_off[0] != 0 || h_pt_off[0] != 0)
+            return ctx->fail("segment %d: offsets must start at 0 and not decrease", s);
+        if (nt > INT32_MAX || np > INT32_MAX) return ctx->fail("segment %d too large", s);
+        if (np == 0) continue;                           // counts stay 0
+        for (int64_t r = 0; r < nt; r += sfm::kRadiusRows)
+            blocks.push_back({h_track_off[s] + r, h_pt_off[s],
+                              static_cast<int32_t>(std::min<int64_t>(sfm::kRadiusRows, nt - r)),
+                              static_cast<int32_t>(np), static_cast<int32_t>(r), 0});
+    }
+    const int64_t rows = h_track_off[n_seg];
+    if (rows > 0 && !d_tracks) return ctx->fail("d_tracks is NULL");
+    if (h_pt_off[n_seg] > 0 && !d_pts) return ctx->fail("d_pts is NULL");
+    if (blocks.size() > static_cast<size_t>(INT32_MAX)) return ctx->fail("too many track blocks");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int32_t nb = static_cast<int32_t>(blocks.size());
+    SFM_CUDA(ctx, ctx->d_rblocks.reserve(blocks.size() + 1));
+    SFM_CUDA(ctx, ctx->d_rcnt.reserve(static_cast<size_t>(rows) + 1));
+    SFM_CUDA(ctx, ctx->d_roff.reserve(static_cast<size_t>(rows) + 1));
+    if (nb > 0)
+        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_rblocks.p, blocks.data(), sizeof(sfm::RadiusBlock) * blocks.size(),
+                                      cudaMemcpyHostToDevice, st));
+    if (rows > 0) SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_rcnt.p, 0, sizeof(long long) * rows, st));
+    const double s_lim = radius_limit(threshold);
+    sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, rows, ctx->d_rcnt.p, ctx->d_roff.p, st,
+                             &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    // match offsets at the segment boundaries: one small copy per segment boundary would be n_seg
+    // copies; the whole offset array is rows + 1 words, read back once
+    ctx->h_meta.resize(static_cast<size_t>(rows) + 1);
+    static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->h_meta.data(), ctx->d_roff.p, sizeof(int64_t) * (rows + 1),
+                                  cudaMemcpyDeviceToHost, st));
+    SFM_CUDA(ctx, cudaStreamSynchronize(st));
+    for (int32_t s = 0; s <= n_seg; ++s) h_seg_off[s] = ctx->h_meta[h_track_off[s]];
+    if (!d_out_track) return 0;
+    const int64_t total = h_seg_off[n_seg];
+    if (total > cap) return 0;   // caller sees h_seg_off[n_seg] > cap and calls again with room
+    // the fill pass writes global positions; segment-local positions follow from h_seg_off
+    sfm::launch_radius_fill(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_roff.p, cap, d_out_track, d_out_pt,
+                            st, &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    SFM_CUDA(ctx, cudaStreamSynchronize(st));
     return 0;
 }
 

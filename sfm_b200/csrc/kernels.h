@@ -81,6 +81,25 @@ void launch_pack(int32_t n_pairs, const int64_t* d_row_off, const int32_t* d_cou
                  const int32_t* d_status, int only_ok, int64_t* d_pack_off, const PackArrays& a,
                  cudaStream_t st, int64_t* launches);
 
+// ---- radius.cu (2-D radius matching of track points)
+constexpr int kRadiusRows = 256;   // tracks per block, one per thread
+struct RadiusBlock {
+    long long row0;    // first track row (global, over all segments)
+    long long pt0;     // first point of the segment (global)
+    int32_t n_rows;    // tracks of this block (<= kRadiusRows)
+    int32_t n_pts;     // points of the segment
+    int32_t track0;    // index of row0 inside its segment
+    int32_t pad;
+};
+// Counts per track row into d_row_cnt[n_rows], then their exclusive scan into d_row_off[n_rows + 1].
+void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
+                         const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
+                         long long* d_row_off, cudaStream_t st, int64_t* launches);
+// (track index in its segment, point index in its segment) of every match, row-major per segment.
+void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
+                        const double* d_pts, double s_lim, const long long* d_row_off, long long cap,
+                        int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st, int64_t* launches);
+
 // ---- ransac.cu
 void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
                           const int64_t* d_row_off, const int32_t* d_mq, const int32_t* d_mt,

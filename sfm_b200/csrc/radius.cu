@@ -1,0 +1,142 @@
+// 2-D radius matching of track points against the points of an image pair.
+//
+// Replaces the dense distance matrix of the reference's find_2d3d_matches
+// (utils/sfm_reconstruction.py:211-213):
+//     distances = np.linalg.norm(valid_track_points[:, None] - other_img_pts, axis=2)
+//     matches = np.where(distances < MATCHING_THRESHOLD)
+// for a whole batch of segments (one segment = the tracks x points of one image pair) at once.
+// The result is the list np.where yields: (track, point) index pairs in row-major order, per
+// segment.  Nothing is materialised but that list: a counting pass, a scan of the per-track
+// counts and a fill pass that repeats the comparison.
+//
+// Exactness.  numpy evaluates sqrt(dx*dx + dy*dy) < thr in f64 with every operation rounded
+// once.  sqrt_rn is monotone, so the test equals  dx*dx + dy*dy < s_lim  with
+// s_lim = min{ s : sqrt_rn(s) >= thr }, which the host finds by bisection over the f64 bit
+// patterns (api.cu).  The device does two subtractions, two products, one sum and one compare,
+// all explicitly round-to-nearest without FMA contraction: the decisions are bit-identical.
+//
+// Layout: tracks f64 [rows, 2] and points f64 [n_pts, 2] concatenated over the segments; block b
+// owns kRadiusRows consecutive tracks of one segment (host-built block list), one track per
+// thread, and walks the segment's points through shared memory in tiles of kRadiusTile (every
+// thread reads the same point: a broadcast).  FP64-pipe bound: 6 f64 operations per (track,
+// point); the bytes are negligible (each point is read from L2 once per 256 tracks).
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "kernels.h"
+
+namespace sfm {
+namespace {
+
+constexpr int kRadiusTile = 1024;   // points staged per pass: 16 KiB of double2
+
+template <bool FILL>
+__global__ void __launch_bounds__(kRadiusRows)
+radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict__ tracks,
+              const double2* __restrict__ pts, double s_lim, long long* __restrict__ row_cnt,
+              const long long* __restrict__ row_off, long long cap, int32_t* __restrict__ out_track,
+              int32_t* __restrict__ out_pt) {
+    __shared__ double2 tile[kRadiusTile];
+    const RadiusBlock b = blocks[blockIdx.x];
+    const int local = static_cast<int>(threadIdx.x);
+    const bool live = local < b.n_rows;
+    const long long row = b.row0 + local;
+    const double2 t = live ? tracks[row] : make_double2(0.0, 0.0);
+    long long n = 0;
+    long long dst = (FILL && live) ? row_off[row] : 0;
+    for (int p0 = 0; p0 < b.n_pts; p0 += kRadiusTile) {
+        const int np = min(kRadiusTile, b.n_pts - p0);
+        __syncthreads();
+        for (int i = local; i < np; i += kRadiusRows) tile[i] = pts[b.pt0 + p0 + i];
+        __syncthreads();
+        if (!live) continue;
+#pragma unroll 4
+        for (int i = 0; i < np; ++i) {
+            const double2 q = tile[i];
+            const double dx = __dsub_rn(t.x, q.x), dy = __dsub_rn(t.y, q.y);
+            const double s = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+            if (s < s_lim) {
+                if (FILL) {
+                    if (dst < cap) {
+                        out_track[dst] = b.track0 + local;
+                        out_pt[dst] = p0 + i;
+                    }
+                    ++dst;
+                } else {
+                    ++n;
+                }
+            }
+        }
+    }
+    if (!FILL && live) row_cnt[row] = n;
+}
+
+// Exclusive scan of n counts into n + 1 offsets by one block (rows are few: a track list, not a
+// descriptor matrix); off[n] = total.
+constexpr int kScanThreads = 1024;
+
+__global__ void __launch_bounds__(kScanThreads) scan_kernel(const long long* __restrict__ cnt, long long n,
+                                                            long long* __restrict__ off) {
+    __shared__ long long warp_sum[kScanThreads / 32];
+    __shared__ long long carry_s;
+    const int tid = static_cast<int>(threadIdx.x), lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (long long base = 0; base < n; base += kScanThreads) {
+        const long long i = base + tid;
+        const long long v = i < n ? cnt[i] : 0;
+        long long x = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) warp_sum[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            long long w = warp_sum[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const long long y = __shfl_up_sync(0xffffffffu, w, d);
+                if (lane >= d) w += y;
+            }
+            warp_sum[lane] = w;   // inclusive over the warps
+        }
+        __syncthreads();
+        const long long carry = carry_s;
+        const long long before = carry + (warp ? warp_sum[warp - 1] : 0) + (x - v);
+        if (i < n) off[i] = before;
+        __syncthreads();
+        if (tid == kScanThreads - 1) carry_s = carry + warp_sum[kScanThreads / 32 - 1];
+        __syncthreads();
+    }
+    if (tid == 0) off[n] = carry_s;
+}
+
+}  // namespace
+
+void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
+                         const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
+                         long long* d_row_off, cudaStream_t st, int64_t* launches) {
+    if (n_blocks > 0) {
+        radius_kernel<false><<<n_blocks, kRadiusRows, 0, st>>>(
+            d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
+            d_row_cnt, nullptr, 0, nullptr, nullptr);
+        ++*launches;
+    }
+    scan_kernel<<<1, kScanThreads, 0, st>>>(d_row_cnt, n_rows, d_row_off);
+    ++*launches;
+}
+
+void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
+                        const double* d_pts, double s_lim, const long long* d_row_off, long long cap,
+                        int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st, int64_t* launches) {
+    if (n_blocks <= 0) return;
+    radius_kernel<true><<<n_blocks, kRadiusRows, 0, st>>>(
+        d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
+        nullptr, d_row_off, cap, d_out_track, d_out_pt);
+    ++*launches;
+}
+
+}  // namespace sfm

@@ -45,7 +45,7 @@ METRICS_DTYPE = np.dtype([
 EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
-    "sfm_ransac_points", "sfm_pack_results", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
+    "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
     "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
@@ -85,6 +85,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_ransac_points.argtypes = [vp, i32, vp, vp, vp, C.POINTER(VerifyParams),
                                       vp, vp, vp, vp, vp, vp]
     lib.sfm_pack_results.argtypes = [vp, i32, vp, vp, vp, i32] + [vp] * 15 + [vp]
+    lib.sfm_radius_match.argtypes = [vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp, i64, vp]
     lib.sfm_launch_count.argtypes = [vp]
     lib.sfm_launch_count.restype = i64
     lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
@@ -316,6 +317,34 @@ class Context:
             self._dev(status, torch.int32) if status is not None else C.c_void_p(0),
             1 if only_ok else 0, *src, C.c_void_p(pack_off.data_ptr()), *dst, self._stream()))
         return pack_off, outs
+
+    # -- 2-D radius matching (find_2d3d_matches)
+    def radius_match(self, track_off, tracks, pt_off, pts, threshold):
+        """tracks f64 [rows,2], pts f64 [n,2] on the device; track_off / pt_off int64 [S+1] (host).
+
+        Returns (seg_off int64 [S+1] numpy, track_idx int32 cuda, pt_idx int32 cuda): for segment s the
+        entries [seg_off[s], seg_off[s+1]) are np.where(dist < threshold) of its tracks x points."""
+        torch = self.torch
+        track_off, pt_off = _i64(track_off), _i64(pt_off)
+        n_seg = len(track_off) - 1
+        if len(pt_off) != n_seg + 1:
+            raise SfmError("track_off and pt_off must have the same length")
+        if tuple(tracks.shape) != (int(track_off[-1]), 2) or tuple(pts.shape) != (int(pt_off[-1]), 2):
+            raise SfmError("tracks / pts must be [rows, 2] matching the offsets")
+        tp = self._dev(tracks, torch.float64) if tracks.numel() else C.c_void_p(0)
+        pp = self._dev(pts, torch.float64) if pts.numel() else C.c_void_p(0)
+        seg_off = np.zeros(n_seg + 1, np.int64)
+        args = (self.h, n_seg, _h(track_off), tp, _h(pt_off), pp, float(threshold), _h(seg_off))
+        cap = max(4 * int(track_off[-1]), 1024)      # a track matches a handful of points at most
+        while True:
+            out_t = self.empty((cap,), torch.int32)
+            out_p = self.empty((cap,), torch.int32)
+            self._check(self.lib.sfm_radius_match(*args, C.c_void_p(out_t.data_ptr()), C.c_void_p(out_p.data_ptr()),
+                                                  cap, self._stream()))
+            total = int(seg_off[-1])
+            if total <= cap:
+                return seg_off, out_t[:total], out_p[:total]
+            cap = total
 
     # -- measurement / debug
     def probe_int8_peak(self, iters=4096):
