@@ -77,6 +77,7 @@ struct sfm_ctx {
     // sfm_radius_match scratch
     DevBuf<sfm::RadiusBlock> d_rblocks;
     DevBuf<long long> d_rcnt, d_roff;
+    DevBuf<int32_t> d_rfirst;
     std::vector<sfm::RadiusBlock> h_rblocks;
 
     int fail(const char* fmt, ...) {
@@ -535,28 +536,32 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     SFM_CUDA(ctx, ctx->d_rblocks.reserve(blocks.size() + 1));
     SFM_CUDA(ctx, ctx->d_rcnt.reserve(static_cast<size_t>(rows) + 1));
     SFM_CUDA(ctx, ctx->d_roff.reserve(static_cast<size_t>(rows) + 1));
+    SFM_CUDA(ctx, ctx->d_rfirst.reserve(static_cast<size_t>(rows) * sfm::kRadiusKeep + 1));
     if (nb > 0)
         SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_rblocks.p, blocks.data(), sizeof(sfm::RadiusBlock) * blocks.size(),
                                       cudaMemcpyHostToDevice, st));
     if (rows > 0) SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_rcnt.p, 0, sizeof(long long) * rows, st));
     const double s_lim = radius_limit(threshold);
-    sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, rows, ctx->d_rcnt.p, ctx->d_roff.p, st,
-                             &ctx->launches);
+    sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, rows, ctx->d_rcnt.p, ctx->d_rfirst.p,
+                             ctx->d_roff.p, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
-    // match offsets at the segment boundaries: one small copy per segment boundary would be n_seg
-    // copies; the whole offset array is rows + 1 words, read back once
-    ctx->h_meta.resize(static_cast<size_t>(rows) + 1);
+    // match offsets at the segment boundaries: gathered on the device, n_seg + 1 words come back
+    const size_t n1 = static_cast<size_t>(n_seg) + 1;
+    SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
     static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
-    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->h_meta.data(), ctx->d_roff.p, sizeof(int64_t) * (rows + 1),
-                                  cudaMemcpyDeviceToHost, st));
+    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p, h_track_off, sizeof(int64_t) * n1, cudaMemcpyHostToDevice, st));
+    sfm::launch_gather_offsets(ctx->d_roff.p, reinterpret_cast<const long long*>(ctx->d_meta.p),
+                               static_cast<int32_t>(n1), reinterpret_cast<long long*>(ctx->d_meta.p + n1), st,
+                               &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_seg_off, ctx->d_meta.p + n1, sizeof(int64_t) * n1, cudaMemcpyDeviceToHost, st));
     SFM_CUDA(ctx, cudaStreamSynchronize(st));
-    for (int32_t s = 0; s <= n_seg; ++s) h_seg_off[s] = ctx->h_meta[h_track_off[s]];
     if (!d_out_track) return 0;
     const int64_t total = h_seg_off[n_seg];
     if (total > cap) return 0;   // caller sees h_seg_off[n_seg] > cap and calls again with room
     // the fill pass writes global positions; segment-local positions follow from h_seg_off
-    sfm::launch_radius_fill(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_roff.p, cap, d_out_track, d_out_pt,
-                            st, &ctx->launches);
+    sfm::launch_radius_fill(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_rfirst.p, ctx->d_roff.p, cap,
+                            d_out_track, d_out_pt, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     SFM_CUDA(ctx, cudaStreamSynchronize(st));
     return 0;

@@ -83,6 +83,7 @@ void launch_pack(int32_t n_pairs, const int64_t* d_row_off, const int32_t* d_cou
 
 // ---- radius.cu (2-D radius matching of track points)
 constexpr int kRadiusRows = 256;   // tracks per block, one per thread
+constexpr int kRadiusKeep = 4;     // hits per track the counting pass keeps for the fill pass
 struct RadiusBlock {
     long long row0;    // first track row (global, over all segments)
     long long pt0;     // first point of the segment (global)
@@ -91,14 +92,19 @@ struct RadiusBlock {
     int32_t track0;    // index of row0 inside its segment
     int32_t pad;
 };
-// Counts per track row into d_row_cnt[n_rows], then their exclusive scan into d_row_off[n_rows + 1].
+// Counts per track row into d_row_cnt[n_rows] (+ the first kRadiusKeep point indices of each row
+// into d_first[n_rows * kRadiusKeep]), then their exclusive scan into d_row_off[n_rows + 1].
 void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
                          const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
-                         long long* d_row_off, cudaStream_t st, int64_t* launches);
+                         int32_t* d_first, long long* d_row_off, cudaStream_t st, int64_t* launches);
+// d_out[i] = d_row_off[d_at[i]]: the match offsets at the segment boundaries.
+void launch_gather_offsets(const long long* d_row_off, const long long* d_at, int32_t n, long long* d_out,
+                           cudaStream_t st, int64_t* launches);
 // (track index in its segment, point index in its segment) of every match, row-major per segment.
 void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                        const double* d_pts, double s_lim, const long long* d_row_off, long long cap,
-                        int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st, int64_t* launches);
+                        const double* d_pts, double s_lim, const int32_t* d_first, const long long* d_row_off,
+                        long long cap, int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st,
+                        int64_t* launches);
 
 // ---- ransac.cu
 void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,

@@ -6,20 +6,24 @@
 //     matches = np.where(distances < MATCHING_THRESHOLD)
 // for a whole batch of segments (one segment = the tracks x points of one image pair) at once.
 // The result is the list np.where yields: (track, point) index pairs in row-major order, per
-// segment.  Nothing is materialised but that list: a counting pass, a scan of the per-track
-// counts and a fill pass that repeats the comparison.
+// segment.  Nothing is materialised but that list: a counting pass that also keeps the first
+// kRadiusKeep hits of every track, a scan of the per-track counts, and a fill pass that copies the
+// kept hits to their place (a track matches a handful of points at most); only blocks that hold a
+// track with more hits than were kept repeat the comparison for those tracks.
 //
 // Exactness.  numpy evaluates sqrt(dx*dx + dy*dy) < thr in f64 with every operation rounded
 // once.  sqrt_rn is monotone, so the test equals  dx*dx + dy*dy < s_lim  with
 // s_lim = min{ s : sqrt_rn(s) >= thr }, which the host finds by bisection over the f64 bit
 // patterns (api.cu).  The device does two subtractions, two products, one sum and one compare,
 // all explicitly round-to-nearest without FMA contraction: the decisions are bit-identical.
+// Rounding is monotone, so rn(dx*dx) >= s_lim already decides "no hit" after three operations.
 //
 // Layout: tracks f64 [rows, 2] and points f64 [n_pts, 2] concatenated over the segments; block b
 // owns kRadiusRows consecutive tracks of one segment (host-built block list), one track per
 // thread, and walks the segment's points through shared memory in tiles of kRadiusTile (every
-// thread reads the same point: a broadcast).  FP64-pipe bound: 6 f64 operations per (track,
-// point); the bytes are negligible (each point is read from L2 once per 256 tracks).
+// thread reads the same point: a broadcast).  FP64-pipe bound: 3 f64 instructions per (track,
+// point), 7 for the few inside the x band; the bytes are negligible (each point is read from L2
+// once per 256 tracks).
 
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -35,8 +39,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(kRadiusRows)
 radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict__ tracks,
               const double2* __restrict__ pts, double s_lim, long long* __restrict__ row_cnt,
-              const long long* __restrict__ row_off, long long cap, int32_t* __restrict__ out_track,
-              int32_t* __restrict__ out_pt) {
+              int32_t* __restrict__ first, const long long* __restrict__ row_off, long long cap,
+              int32_t* __restrict__ out_track, int32_t* __restrict__ out_pt) {
     __shared__ double2 tile[kRadiusTile];
     const RadiusBlock b = blocks[blockIdx.x];
     const int local = static_cast<int>(threadIdx.x);
@@ -45,17 +49,33 @@ radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict_
     const double2 t = live ? tracks[row] : make_double2(0.0, 0.0);
     long long n = 0;
     long long dst = (FILL && live) ? row_off[row] : 0;
+    bool scan = live;
+    if (FILL) {
+        const long long cnt = live ? row_off[row + 1] - dst : 0;
+        scan = cnt > kRadiusKeep;
+        if (!scan)
+            for (int i = 0; i < static_cast<int>(cnt); ++i)
+                if (dst + i < cap) {
+                    out_track[dst + i] = b.track0 + local;
+                    out_pt[dst + i] = first[row * kRadiusKeep + i];
+                }
+        if (!__syncthreads_or(scan)) return;
+    }
     for (int p0 = 0; p0 < b.n_pts; p0 += kRadiusTile) {
         const int np = min(kRadiusTile, b.n_pts - p0);
         __syncthreads();
         for (int i = local; i < np; i += kRadiusRows) tile[i] = pts[b.pt0 + p0 + i];
         __syncthreads();
-        if (!live) continue;
+        if (!scan) continue;
 #pragma unroll 4
         for (int i = 0; i < np; ++i) {
             const double2 q = tile[i];
-            const double dx = __dsub_rn(t.x, q.x), dy = __dsub_rn(t.y, q.y);
-            const double s = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+            const double dx = __dsub_rn(t.x, q.x);
+            const double sx = __dmul_rn(dx, dx);
+            // rn(sx + sy) >= sx for sy >= 0: a point outside the band in x alone is decided here
+            if (!(sx < s_lim)) continue;
+            const double dy = __dsub_rn(t.y, q.y);
+            const double s = __dadd_rn(sx, __dmul_rn(dy, dy));
             if (s < s_lim) {
                 if (FILL) {
                     if (dst < cap) {
@@ -64,6 +84,7 @@ radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict_
                     }
                     ++dst;
                 } else {
+                    if (n < kRadiusKeep) first[row * kRadiusKeep + n] = p0 + i;
                     ++n;
                 }
             }
@@ -114,15 +135,28 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const long long* __r
     if (tid == 0) off[n] = carry_s;
 }
 
+__global__ void gather_offsets_kernel(const long long* __restrict__ row_off, const long long* __restrict__ at,
+                                      int n, long long* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = row_off[at[i]];
+}
+
 }  // namespace
+
+void launch_gather_offsets(const long long* d_row_off, const long long* d_at, int32_t n, long long* d_out,
+                           cudaStream_t st, int64_t* launches) {
+    if (n <= 0) return;
+    gather_offsets_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_row_off, d_at, n, d_out);
+    ++*launches;
+}
 
 void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
                          const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
-                         long long* d_row_off, cudaStream_t st, int64_t* launches) {
+                         int32_t* d_first, long long* d_row_off, cudaStream_t st, int64_t* launches) {
     if (n_blocks > 0) {
         radius_kernel<false><<<n_blocks, kRadiusRows, 0, st>>>(
             d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
-            d_row_cnt, nullptr, 0, nullptr, nullptr);
+            d_row_cnt, d_first, nullptr, 0, nullptr, nullptr);
         ++*launches;
     }
     scan_kernel<<<1, kScanThreads, 0, st>>>(d_row_cnt, n_rows, d_row_off);
@@ -130,12 +164,13 @@ void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const do
 }
 
 void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                        const double* d_pts, double s_lim, const long long* d_row_off, long long cap,
-                        int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st, int64_t* launches) {
+                        const double* d_pts, double s_lim, const int32_t* d_first, const long long* d_row_off,
+                        long long cap, int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st,
+                        int64_t* launches) {
     if (n_blocks <= 0) return;
     radius_kernel<true><<<n_blocks, kRadiusRows, 0, st>>>(
         d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
-        nullptr, d_row_off, cap, d_out_track, d_out_pt);
+        nullptr, const_cast<int32_t*>(d_first), d_row_off, cap, d_out_track, d_out_pt);
     ++*launches;
 }
 

@@ -60,17 +60,21 @@ def main():
         reps += 1
     cpu_s = (time.perf_counter() - t0) / reps
     cpu_rate = samp * npnt / cpu_s
-    # pass 1 (count) and pass 2 (fill) both evaluate every (track, point): 2 x 6 f64 operations
-    flops = 2 * 6 * tests / (ms * 1e-3)
+    # the counting pass evaluates every (track, point) once: 3 f64 instructions (sub, mul, compare;
+    # 4 more for the ~0.4 % inside the x band), none of them an FMA; the fill pass copies kept hits.
+    # The FP64 pipe issues one instruction per FMA slot: instruction peak = nominal 37 TFLOP/s / 2.
+    flops = 3 * tests / (ms * 1e-3)
     print(json.dumps({
         "metric": "track_point_tests_per_sec", "value": tests / (ms * 1e-3), "unit": "tests/s", "ms": ms,
         "workload": f"{n_seg} segments x {nt} tracks x {npnt} points, threshold 2.0", "hits": int(so[-1]),
         "gpu_launches_per_call": int(launches),
         "e2e": {"value": tests / (e2e_ms * 1e-3), "unit": "tests/s", "ms": e2e_ms,
                 "h2d_bytes": int(tracks.nbytes + pts.nbytes), "d2h_bytes": int(8 * so[-1] + so.nbytes)},
-        "roofline": {"bound": "fp64 pipe", "achieved": flops / 1e12, "peak": 37.0, "unit": "TFLOP/s",
-                     "frac": flops / 1e12 / 37.0,
-                     "note": "2 passes x (2 sub, 2 mul, 1 add, 1 compare) per test; nominal B200 FP64 vector peak"},
+        "roofline": {"bound": "fp64 pipe", "achieved": flops / 1e12, "peak": 18.5, "unit": "T f64 instr/s",
+                     "frac": flops / 1e12 / 18.5,
+                     "note": "sub, mul, compare per test, the rest only inside the x band (no FMA: each step rounds as numpy "
+                             "does); the ms include the scan, the offset read-back and the fill pass; "
+                             "peak = nominal B200 FP64 37 TFLOP/s / 2 flops per FMA slot"},
         "cpu_baseline": {"value": cpu_rate, "unit": "tests/s", "cores": 1, "kind": "reference",
                          "sample": f"np.linalg.norm(t[:, None] - p, axis=2) < 2.0 + np.where on {samp} tracks x {npnt} "
                                    "points (utils/sfm_reconstruction.py:211-213), repeated for 10 s"},
