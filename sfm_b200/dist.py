@@ -2,15 +2,41 @@
 
 The hot path shards by image PAIR: pairs are independent, so the
 only exchanges are (1) replicating the descriptor set on every GPU once (NCCL
-all-gather over NVLink) and (2) gathering the per-pair results on rank 0, which
-alone writes files -- outputs are identical to a 1-GPU run.  No collective runs
-during compute.  Works with the gloo backend on CPU tensors for tests.
+all-gather over NVLink) and (2) collecting results: ``ImageMatcher`` lets every rank
+write the files of its own pairs (file names are per pair, so the directory equals
+a 1-GPU run's) and gathers only the CSV rows on rank 0 (``gather_rows``);
+``gather_batch_results`` brings whole match lists to rank 0 for callers that want
+them in one process.  No collective runs during compute.  Works with the gloo
+backend on CPU tensors for tests.
 """
 from __future__ import annotations
 
 import numpy as np
 import torch
 import torch.distributed as dist
+
+
+def rank_world(group=None):
+    """(rank, world) of this process; (0, 1) outside torch.distributed."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def all_gather_objects(obj, group=None):
+    """Small picklable host objects from every rank, in rank order, on every rank."""
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, obj, group=group)
+    return out
+
+
+def gather_rows(rows: list, group=None):
+    """Per-pair result rows (CSV dicts) of every rank concatenated in rank order on rank 0 --
+    pair order, because ranks own contiguous ranges of the pair list.  None elsewhere."""
+    parts = all_gather_objects(rows, group)
+    if dist.get_rank(group) != 0:
+        return None
+    return [r for part in parts for r in part]
 
 
 def image_blocks(n_images: int, world: int):

@@ -26,6 +26,7 @@ from types import SimpleNamespace
 
 import numpy as np
 
+from . import dist as D
 from . import features as feat
 from . import lib as L
 
@@ -228,12 +229,13 @@ class ImageMatcher:
                 pool.shutdown(wait=True)
         return rows
 
-    def collect_features(self, start_idx, end_idx, mask=False):
-        """Features of every existing image id in the inclusive range, extracted ONCE per image
-        (hoisted out of the reference's per-pair loop, :265-266): {id: (path, kps f32 [n,2], desc u8 [n,128])}."""
+    def collect_features(self, start_idx, end_idx, mask=False, ids=None):
+        """Features of every existing image id in the inclusive range (or of `ids`), extracted ONCE
+        per image (hoisted out of the reference's per-pair loop, :265-266):
+        {id: (path, kps f32 [n,2], desc u8 [n,128])}."""
         import cv2
         feats = {}
-        for i in range(start_idx, end_idx + 1):
+        for i in (range(start_idx, end_idx + 1) if ids is None else ids):
             p = feat.find_image(self.image_dir, i)
             if p is None:
                 continue
@@ -274,12 +276,71 @@ class ImageMatcher:
 
     def process_image_range(self, start_idx, end_idx, mask=False):
         """utils/find_matches.py:329-350: all pairs i<j of the existing images in the inclusive
-        range; never raises for a bad pair.  `mask` is used for truthiness only (main.py:199)."""
+        range; never raises for a bad pair.  `mask` is used for truthiness only (main.py:199).
+        Under torch.distributed (one process per GPU) the images and the pairs are split over the
+        ranks."""
+        rank, world = D.rank_world()
+        if world > 1:
+            return self._process_image_range_ranks(start_idx, end_idx, mask, rank, world)
         self.process_features(self.collect_features(start_idx, end_idx, mask), start_idx, end_idx)
+
+    def _process_image_range_ranks(self, start_idx, end_idx, mask, rank, world):
+        """One process per GPU: rank r extracts the features of the r-th contiguous block of images,
+        one all-gather replicates descriptors and keypoints on every GPU, the pair list is cut into
+        contiguous ranges of equal n_i * n_j, every rank matches its range and writes the files of
+        its own pairs (names are per pair: the directories equal a 1-GPU run's), and the CSV rows
+        meet on rank 0 in pair order.  No collective runs between upload and row gather."""
+        import torch
+        if torch.cuda.is_available():
+            torch.cuda.set_device(self.device)
+        ids = [i for i in range(start_idx, end_idx + 1) if feat.find_image(self.image_dir, i) is not None]
+        b0, b1 = D.image_blocks(len(ids), world)[rank]
+        mine = self.collect_features(start_idx, end_idx, mask, ids=ids[b0:b1])
+        ok = D.all_gather_objects(sorted(mine))                    # an image that failed is absent everywhere
+        ids = [i for part in ok for i in part]
+        my_ids = ok[rank]
+        for i in my_ids:
+            d = mine[i][2]
+            if len(d) and not np.array_equal(d.astype(np.uint8).astype(d.dtype), d):
+                raise ValueError("descriptors must be integer-valued in 0..255 (SIFT)")
+        eng = self._get_engine()
+        dev = eng.ctx.device
+        ld = np.concatenate([mine[i][2].astype(np.uint8).reshape(-1, 128) for i in my_ids] or [np.zeros((0, 128), np.uint8)])
+        lk = np.concatenate([np.asarray(mine[i][1], np.float32).reshape(-1, 2) for i in my_ids] or [np.zeros((0, 2), np.float32)])
+        desc, kps, off = D.replicate_images(torch.from_numpy(ld).to(dev), torch.from_numpy(lk).to(dev),
+                                            [len(mine[i][2]) for i in my_ids])
+        pos = {i: n for n, i in enumerate(ids)}
+        paths = {i: feat.find_image(self.image_dir, i) for i in ids}
+        names, pairs = [], []
+        for i in range(start_idx, end_idx):
+            for j in range(i + 1, end_idx + 1):
+                if i in pos and j in pos:
+                    names.append((paths[i], paths[j], f"pair_{i}_{j}"))
+                    pairs.append((pos[i], pos[j]))
+        rows = []
+        if pairs:
+            pairs = np.array(pairs, np.int32)
+            lo, hi = D.partition_pairs(pairs, np.diff(off), world)[rank]
+            try:
+                eng.set_images(desc, kps, off)
+                if hi > lo:
+                    res = eng.match_pairs(pairs[lo:hi], only_ok=True)
+                    self.last_batch = res
+                    self.last_names = names[lo:hi]
+                    rows = self._emit(res, names[lo:hi])
+            except L.SfmError:
+                raise
+            except Exception as e:
+                logging.error(f"Error processing pairs: {e}")
+        rows = D.gather_rows(rows)
+        if rows is not None:
+            self.results.extend(rows)
 
     def save_results(self, output_csv):
         """utils/find_matches.py:352-364 (raises KeyError with zero rows, as the reference does)."""
         import pandas as pd
+        if D.rank_world()[0] != 0:
+            return                                  # the rows were gathered on rank 0
         df = pd.DataFrame(self.results)
         df.to_csv(output_csv, index=False)
         logging.info(f"Results saved to {output_csv}")
@@ -309,8 +370,18 @@ def _verification_dict(m, mask, sym):
     }
 
 
-def run_preprocessing(data_dir, start_idx=0, end_idx=35, mask=None, device=0) -> bool:
-    """``main.py preprocess`` (main.py:189-213): returns the stage's bool."""
+def run_preprocessing(data_dir, start_idx=0, end_idx=35, mask=None, device=None) -> bool:
+    """``main.py preprocess`` (main.py:189-213): returns the stage's bool.  Under ``torchrun`` the
+    process group is joined (NCCL) and the GPU is the local rank's."""
+    import os
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", 0))
+    if int(os.environ.get("WORLD_SIZE", 1)) > 1:
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            torch.cuda.set_device(device)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", device))
     try:
         matcher = ImageMatcher(data_dir, device=device)
         matcher.process_image_range(start_idx, end_idx, mask)

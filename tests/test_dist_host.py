@@ -76,6 +76,18 @@ def _worker(rank, world, port, ret):
             ok = ok and torch.equal(g["F"][:, 0], torch.arange(len(pairs), dtype=torch.float64))
         else:
             ok = ok and g is None
+        # CSV rows of ImageMatcher's rank path: pair order on rank 0, a rank may have none
+        ok = ok and D.rank_world() == (rank, world)
+        rows = [{"pair_name": f"pair_{a}_{b}", "num_matches": int(a) * 10 + int(b)} for a, b in pairs[lo:hi]]
+        if rank == 1:
+            rows = rows[:0] if hi - lo < 2 else rows
+        got = D.gather_rows(rows)
+        lists = D.all_gather_objects(sorted(range(b0, b1)))
+        ok = ok and [i for part in lists for i in part] == list(range(len(counts)))
+        if rank == 0:
+            ok = ok and [r["pair_name"] for r in got] == [f"pair_{a}_{b}" for a, b in pairs]
+        else:
+            ok = ok and got is None
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
@@ -89,6 +101,10 @@ def test_replicate_and_gather_world2_gloo():
         ret = mgr.dict()
         mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
         assert dict(ret) == {0: True, 1: True}
+
+
+def test_rank_world_outside_distributed():
+    assert D.rank_world() == (0, 1)
 
 
 def test_c_abi_exports_every_declared_symbol():
@@ -108,3 +124,20 @@ def test_c_abi_exports_every_declared_symbol():
     if not torch.cuda.is_available():
         assert so.sfm_create(0, ctypes.byref(h)) != 0          # fails loudly without a device
         assert b"CUDA" in so.sfm_last_error(None) or b"device" in so.sfm_last_error(None)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+def test_preprocess_two_ranks_equal_one_rank():
+    """`python -m sfm_b200.preprocess` under torchrun with 2 ranks writes the same files and CSV as one
+    process (tests/run_ranks_compare.py); needs two GPUs."""
+    import json
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    p = subprocess.run([sys.executable, str(ROOT / "tests" / "run_ranks_compare.py"), "2", "8"], capture_output=True,
+                       text=True, timeout=800)
+    assert p.returncode == 0, p.stderr[-3000:]
+    out = json.loads(p.stdout.strip().splitlines()[-1])
+    assert out["check"] == "preprocess outputs identical" and out["files_compared"] > 20
