@@ -306,14 +306,14 @@ def run_b200(args):
             return sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
                                                         "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1",
                                                         "pts2"))
-        local = eng.match_pairs_device(my_pairs)               # results stay on the device ...
-        g = D.gather_batch_results(local)                      # ... match lists gathered back to rank 0 (NCCL)
-        nbytes = 0
-        if g is not None:                                      # rank 0 alone copies them to the host
-            flat = {k: g[k] for k in ("pairs", "status", "count", "metrics", "F", "pack_off")}
-            flat.update({"dense_" + k: v for k, v in g["dense"].items()})
-            host = eng._to_host(flat)
-            nbytes = sum(a.nbytes for a in host.values())
+        # N > 1, as ImageMatcher's rank path: every rank brings the match lists of ITS pairs to its own
+        # host memory (it writes those files); only the per-pair status / metrics rows meet on rank 0
+        res = eng.match_pairs(my_pairs)
+        nbytes = sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
+                                                      "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1", "pts2"))
+        rows = torch.from_numpy(np.ascontiguousarray(res.metrics).view(np.uint8).reshape(len(my_pairs), -1)).to(dev)
+        D.gather_to_root(rows)
+        D.gather_to_root(torch.from_numpy(np.ascontiguousarray(res.status)).to(dev))
         return nbytes
 
     e2e_step()
@@ -324,6 +324,10 @@ def run_b200(args):
         d2h = e2e_step()
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0) / args.steps
+    if world > 1:                                              # bytes of all ranks
+        t_b = torch.tensor([d2h, h2d], dtype=torch.int64, device=dev)
+        dist.all_reduce(t_b)
+        d2h, h2d = int(t_b[0].item()), int(t_b[1].item())
     e2e_pairs_s = len(pairs) / e2e_s
 
     # ---------------------------------------------------------- CPU baseline (rank 0, N = 1)

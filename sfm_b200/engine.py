@@ -64,6 +64,7 @@ class PairEngine:
         self.max_rows = int(max_rows_per_chunk)
         self.counts = None
         self._bufs = {}
+        self._copy_stream = None     # device -> host copies of match_pairs
 
     # ------------------------------------------------------------ image set
     def set_images(self, desc, kps, offsets):
@@ -175,30 +176,85 @@ class PairEngine:
         """Public call: pair list in, host-side verified matches out (chunked)."""
         torch = self.torch
         pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
         parts = []
-        for lo, hi in self._chunks(pairs):
-            d = self._match_chunk(pairs[lo:hi], only_ok)
-            # device -> pinned host, asynchronously; two synchronisations per chunk (the dense
-            # arrays' length is only known once pack_off has arrived)
-            small = self._to_host(dict(status=d["status"], count=d["count"], metrics=d["metrics"], F=d["F"],
-                                       pack_off=d["pack_off"]))
-            total = int(small["pack_off"][-1])
-            dn = d["dense"]
-            dense = self._to_host({k: dn[k][:total] for k in ("mq", "mt", "md2", "mask", "sym", "pts1", "pts2")})
+
+        n_chunks = sum(1 for _ in self._chunks(pairs))
+        DENSE = (("mq", "query_idx"), ("mt", "train_idx"), ("md2", "sq_dist"), ("mask", "inlier_mask"),
+                 ("sym", "sym_err"), ("pts1", "pts1"), ("pts2", "pts2"))
+        arena = {}                  # several chunks: the dense arrays land in ONE pinned array each
+        state = dict(base=0, pairs_done=0)
+
+        def reserve(dn, total, n_here):
+            """Room for `total` more dense entries (of n_here pairs); capacity from the density so far."""
+            need = state["base"] + total
+            for k, _ in DENSE:
+                cur = arena.get(k)
+                if cur is not None and cur.shape[0] >= need:
+                    continue
+                done_p = state["pairs_done"] + n_here
+                cap = max(need, int(need * len(pairs) / max(done_p, 1) * 1.15) + 1024)
+                new = torch.empty((cap,) + tuple(dn[k].shape[1:]), dtype=dn[k].dtype, pin_memory=True)
+                if cur is not None:
+                    new[:state["base"]] = cur[:state["base"]]
+                arena[k] = new
+
+        def finish(d, done, lo, hi):
+            # device -> pinned host on the copy stream, asynchronously; two synchronisations per chunk
+            # (the dense arrays' length is only known once pack_off has arrived)
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(done)
+                small = self._to_host(dict(status=d["status"], count=d["count"], metrics=d["metrics"], F=d["F"],
+                                           pack_off=d["pack_off"]))
+                total = int(small["pack_off"][-1])
+                dn = d["dense"]
+                if n_chunks == 1:
+                    dense = self._to_host({k: dn[k][:total] for k, _ in DENSE})
+                else:
+                    reserve(dn, total, hi - lo)
+                    b = state["base"]
+                    for k, _ in DENSE:
+                        arena[k][b:b + total].copy_(dn[k][:total], non_blocking=True)
+                    self._copy_stream.synchronize()
+                    dense = None
             nt_small = self.counts[pairs[lo:hi, 1]] < 2
             nq_zero = self.counts[pairs[lo:hi, 0]] < 1
             # reference gate :268 and the Nt<2 failure of the ratio loop (:151)
             status = np.where(nt_small | nq_zero, L.PAIR_TOO_FEW_FEATURES, small["status"]).astype(np.int32)
-            parts.append(dict(
-                pairs=pairs[lo:hi], status=status, count=small["count"],
-                metrics=L.metrics_to_numpy(small["metrics"]), F=small["F"].reshape(-1, 3, 3),
-                pack_off=small["pack_off"], query_idx=dense["mq"], train_idx=dense["mt"], sq_dist=dense["md2"],
-                inlier_mask=dense["mask"].view(np.bool_), sym_err=dense["sym"], pts1=dense["pts1"],
-                pts2=dense["pts2"]))
-        return _concat(parts, pairs)
+            part = dict(pairs=pairs[lo:hi], status=status, count=small["count"],
+                        metrics=L.metrics_to_numpy(small["metrics"]), F=small["F"].reshape(-1, 3, 3),
+                        pack_off=small["pack_off"])
+            if dense is not None:
+                part.update({name: dense[k] for k, name in DENSE})
+                part["inlier_mask"] = part["inlier_mask"].view(np.bool_)
+            parts.append(part)
+            state["base"] += total
+            state["pairs_done"] += hi - lo
+
+        # chunk c's kernels are queued before chunk c-1's results are fetched: the copies (and this
+        # thread's waits) overlap the next chunk's compute.  Everything fetched is a per-chunk
+        # allocation except the count arena, which is cloned.
+        pending = None
+        for lo, hi in self._chunks(pairs):
+            d = self._match_chunk(pairs[lo:hi], only_ok)
+            d["count"] = d["count"].clone()
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(self.device))
+            if pending is not None:
+                finish(*pending)
+            pending = (d, done, lo, hi)
+        if pending is not None:
+            finish(*pending)
+        dense_all = None
+        if n_chunks > 1:
+            dense_all = {name: arena[k][:state["base"]].numpy() for k, name in DENSE}
+            dense_all["inlier_mask"] = dense_all["inlier_mask"].view(np.bool_)
+        return _concat(parts, pairs, dense_all)
 
 
-def _concat(parts, pairs) -> PairBatchResult:
+def _concat(parts, pairs, dense_all=None) -> PairBatchResult:
+    """dense_all: the dense arrays of all parts, already contiguous (match_pairs with several chunks)."""
     if not parts:
         z = np.zeros(0, np.int32)
         return PairBatchResult(pairs=pairs, status=z, count=z, metrics=np.zeros(0, L.METRICS_DTYPE),
@@ -215,7 +271,8 @@ def _concat(parts, pairs) -> PairBatchResult:
     for q in parts:
         offs.append(q["pack_off"][1:] + base)
         base += int(q["pack_off"][-1])
-    cat = lambda k: np.concatenate([q[k] for q in parts])   # noqa: E731
+    cat = lambda k: dense_all[k] if dense_all is not None and k in dense_all else \
+        np.concatenate([q[k] for q in parts])   # noqa: E731
     return PairBatchResult(
         pairs=pairs, status=cat("status"), count=cat("count"), metrics=cat("metrics"), F=cat("F"),
         pack_off=np.concatenate(offs), query_idx=cat("query_idx"), train_idx=cat("train_idx"),

@@ -111,3 +111,30 @@ def test_bunny_range_files_and_parity_with_oracle(tmp_path, golden_dir):
         assert row["num_matches"] == len(q) and row["num_inliers"] == int(fz["mask"].sum())
         assert abs(row["inlier_ratio"] - v["metrics"]["inlier_ratio"]) < 1e-12
         assert np.isclose(row["reprojection_error"], v["metrics"]["reprojection_error"], rtol=1e-4)
+
+
+@pytest.mark.gpu
+def test_match_pairs_chunked_equals_single_chunk():
+    """PairEngine.match_pairs with a tiny chunk size (many chunks, results fetched behind the next
+    chunk's compute into one pinned arena that has to grow) returns exactly the single-chunk result."""
+    from sfm_b200 import synth
+    from sfm_b200.engine import PairEngine
+    sizes = [900, 400, 1300, 700, 650, 1000, 300, 820]
+    s = synth.make_image_set(len(sizes), sizes, seed=21, shared_frac=0.6, tie_frac=0.02)
+    pairs = np.array([(i, j) for i in range(len(sizes)) for j in range(i + 1, len(sizes))], np.int32)
+    # later pairs carry more matches than the first ones would predict: forces the arena to grow
+    order = np.argsort([sizes[i] for i, _ in pairs], kind="stable")
+    pairs = pairs[order]
+    one = PairEngine(0)
+    one.upload_images(s.desc, s.kps, s.offsets.numpy())
+    a = one.match_pairs(pairs, only_ok=True)       # passing pairs only: every packed array is defined
+    many = PairEngine(0, max_rows_per_chunk=1500)
+    many.upload_images(s.desc, s.kps, s.offsets.numpy())
+    assert sum(1 for _ in many._chunks(pairs)) > 8
+    b = many.match_pairs(pairs, only_ok=True)
+    assert int(a.pack_off[-1]) > 100 and int((a.status == 0).sum()) >= 10
+    for f in ("status", "count", "F", "pack_off", "query_idx", "train_idx", "sq_dist", "inlier_mask", "sym_err",
+              "pts1", "pts2"):
+        x, y = getattr(a, f), getattr(b, f)
+        assert x.dtype == y.dtype and x.shape == y.shape and np.array_equal(x, y, equal_nan=True), f
+    assert a.metrics.tobytes() == b.metrics.tobytes()
