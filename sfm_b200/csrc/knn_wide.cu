@@ -171,8 +171,12 @@ __device__ __forceinline__ void fold_chunk(Trk& s, const uint32_t (&acc)[16], in
         return;
     }
     const uint32_t sb = s.k2 & 1u;
-    const uint32_t key = SH0 ? (static_cast<uint32_t>(m) * 512u - 2u * c) + (ut + sb)
-                             : (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + ut + (sb - 2u * c);
+    // low key bits: (uidrev of chunk c) << 1 | slot.  The units of a tile count down from a value whose
+    // low three bits are 111 (n_units is a multiple of 8), so ut - 2c == ut ^ 2c: a warp-uniform value
+    // (uniform datapath) that one LOP3 merges with the slot bit; the rest is one IMAD on the FMA pipe.
+    const uint32_t low = sb | (ut ^ (2u * c));
+    const uint32_t key = SH0 ? static_cast<uint32_t>(m) * 512u + low
+                             : (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + low;
     if (key > s.k2) {
         const uint32_t dst = slots + sb * kSlotStride;
 #pragma unroll
@@ -319,7 +323,9 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     if (smem_u32(smem_raw) & 1023u) __trap();   // SWIZZLE_128B tiles need 1024-byte alignment
     SmemLayout sm(smem_raw);
-    const int warp = threadIdx.x >> 5;
+    // broadcast from lane 0: tells the compiler the warp index (and every TMEM address derived from it)
+    // is warp-uniform, so it lives in uniform registers instead of being re-materialised per tcgen05.ld
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
 
     if (warp == kProducerWarp && lane == 0) {
@@ -348,7 +354,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *sm.tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *sm.tmem_slot, 0);
 
     if (warp == kProducerWarp) {
         // warp-convergent loop, TMA issue predicated on one elected lane (see knn.cu)
