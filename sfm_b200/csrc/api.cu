@@ -39,6 +39,51 @@ struct DevBuf {
     }
 };
 
+// Host -> device copies of per-call metadata (pair lists, offsets).  cudaMemcpyAsync from pageable
+// memory waits for the stream's earlier work before it returns, which serialises the host with the
+// previous kernel (1 ms of launch gaps per step on a slow host).  A small ring of pinned staging
+// slots makes the copies truly asynchronous; a slot is reused only after its copy has executed.
+struct PinnedRing {
+    static constexpr int kSlots = 32;
+    struct Slot {
+        void* p = nullptr;
+        size_t cap = 0;
+        cudaEvent_t ev = nullptr;
+        bool busy = false;
+    } slot[kSlots];
+    int next = 0;
+    cudaError_t copy(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+        if (bytes == 0) return cudaSuccess;
+        Slot& s = slot[next];
+        next = (next + 1) % kSlots;
+        cudaError_t e;
+        if (!s.ev && (e = cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if (s.busy && (e = cudaEventSynchronize(s.ev)) != cudaSuccess) return e;
+        s.busy = false;
+        if (s.cap < bytes) {
+            if (s.p) cudaFreeHost(s.p);
+            s.p = nullptr;
+            s.cap = 0;
+            const size_t want = bytes + bytes / 2 + 4096;
+            if ((e = cudaMallocHost(&s.p, want)) != cudaSuccess) return e;
+            s.cap = want;
+        }
+        std::memcpy(s.p, src, bytes);
+        if ((e = cudaMemcpyAsync(dst, s.p, bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(s.ev, st)) != cudaSuccess) return e;
+        s.busy = true;
+        return cudaSuccess;
+    }
+    void release() {
+        for (Slot& s : slot) {
+            if (s.busy) cudaEventSynchronize(s.ev);
+            if (s.p) cudaFreeHost(s.p);
+            if (s.ev) cudaEventDestroy(s.ev);
+            s = Slot{};
+        }
+    }
+};
+
 }  // namespace
 
 struct sfm_ctx {
@@ -73,6 +118,7 @@ struct sfm_ctx {
     DevBuf<int64_t> d_meta;      // blk_prefix | row_off | row_off_rev
     DevBuf<sfm::WorkItem> d_work;
     std::vector<int64_t> h_meta;
+    PinnedRing ring;             // staging of host metadata
 
     // sfm_radius_match scratch
     DevBuf<sfm::RadiusBlock> d_rblocks;
@@ -120,16 +166,14 @@ int stage_meta(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int6
     SFM_CUDA(ctx, ctx->d_pairs.reserve(static_cast<size_t>(n_pairs) * 2 + 2));
     SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
     if (n_pairs > 0)
-        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_pairs.p, h_pairs, sizeof(int32_t) * 2 * n_pairs,
-                                      cudaMemcpyHostToDevice, st));
+        SFM_CUDA(ctx, ctx->ring.copy(ctx->d_pairs.p, h_pairs, sizeof(int32_t) * 2 * n_pairs, st));
     const int64_t* src[3] = {a, b, c};
     const int64_t** dst[3] = {da, db, dc};
     for (int i = 0; i < 3; ++i) {
         if (!dst[i]) continue;
         *dst[i] = nullptr;
         if (!src[i]) continue;
-        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p + i * n1, src[i], sizeof(int64_t) * n1,
-                                      cudaMemcpyHostToDevice, st));
+        SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p + i * n1, src[i], sizeof(int64_t) * n1, st));
         *dst[i] = ctx->d_meta.p + i * n1;
     }
     return 0;
@@ -222,6 +266,11 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_pairs.release();
     ctx->d_meta.release();
     ctx->d_work.release();
+    ctx->d_rblocks.release();
+    ctx->d_rcnt.release();
+    ctx->d_roff.release();
+    ctx->d_rfirst.release();
+    ctx->ring.release();
     delete ctx;
 }
 
@@ -428,7 +477,7 @@ static int points_entry(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_off, con
     if (params) prm = *params; else sfm_default_params(&prm);
     const size_t n1 = static_cast<size_t>(n_pairs) + 1;
     SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
-    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p, h_off, sizeof(int64_t) * n1, cudaMemcpyHostToDevice, st));
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p, h_off, sizeof(int64_t) * n1, st));
     int r = sfm::launch_ransac_verify(n_pairs, ctx->d_meta.p, nullptr, nullptr, d_pts1, d_pts2, d_F_in, prm,
                                       d_F, d_mask, d_sym, d_metrics, d_status, st, &ctx->launches);
     if (r) return ctx->fail("ransac launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
@@ -473,8 +522,7 @@ int sfm_pack_results(sfm_ctx* ctx, int32_t n_pairs, const int64_t* h_row_off, co
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t n1 = static_cast<size_t>(n_pairs) + 1;
     SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
-    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p + n1, h_row_off, sizeof(int64_t) * n1,
-                                  cudaMemcpyHostToDevice, st));
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p + n1, h_row_off, sizeof(int64_t) * n1, st));
     sfm::PackArrays a{d_mq, d_mt, d_md2, d_mask, d_sym, d_pts1, d_pts2,
                       o_mq, o_mt, o_md2, o_mask, o_sym, o_pts1, o_pts2};
     sfm::launch_pack(n_pairs, ctx->d_meta.p + n1, d_count, d_status, only_ok ? 1 : 0, d_pack_off, a, st,
@@ -538,8 +586,7 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     SFM_CUDA(ctx, ctx->d_roff.reserve(static_cast<size_t>(rows) + 1));
     SFM_CUDA(ctx, ctx->d_rfirst.reserve(static_cast<size_t>(rows) * sfm::kRadiusKeep + 1));
     if (nb > 0)
-        SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_rblocks.p, blocks.data(), sizeof(sfm::RadiusBlock) * blocks.size(),
-                                      cudaMemcpyHostToDevice, st));
+        SFM_CUDA(ctx, ctx->ring.copy(ctx->d_rblocks.p, blocks.data(), sizeof(sfm::RadiusBlock) * blocks.size(), st));
     if (rows > 0) SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_rcnt.p, 0, sizeof(long long) * rows, st));
     const double s_lim = radius_limit(threshold);
     sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, rows, ctx->d_rcnt.p, ctx->d_rfirst.p,
@@ -549,7 +596,7 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     const size_t n1 = static_cast<size_t>(n_seg) + 1;
     SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
     static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
-    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_meta.p, h_track_off, sizeof(int64_t) * n1, cudaMemcpyHostToDevice, st));
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p, h_track_off, sizeof(int64_t) * n1, st));
     sfm::launch_gather_offsets(ctx->d_roff.p, reinterpret_cast<const long long*>(ctx->d_meta.p),
                                static_cast<int32_t>(n1), reinterpret_cast<long long*>(ctx->d_meta.p + n1), st,
                                &ctx->launches);
