@@ -564,7 +564,9 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     if (std::isnan(threshold)) return ctx->fail("threshold is NaN");
     auto& blocks = ctx->h_rblocks;
     blocks.clear();
+    ctx->h_meta.assign(static_cast<size_t>(n_seg) + 1, 0);       // blocks before each segment
     for (int32_t s = 0; s < n_seg; ++s) {
+        ctx->h_meta[s] = static_cast<int64_t>(blocks.size());
         const int64_t nt = h_track_off[s + 1] - h_track_off[s], np = h_pt_off[s + 1] - h_pt_off[s];
         if (nt < 0 || np < 0 || h_track_off[0] != 0 || h_pt_off[0] != 0)
             return ctx->fail("segment %d: offsets must start at 0 and not decrease", s);
@@ -575,6 +577,7 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
                               static_cast<int32_t>(std::min<int64_t>(sfm::kRadiusRows, nt - r)),
                               static_cast<int32_t>(np), static_cast<int32_t>(r), 0});
     }
+    ctx->h_meta[n_seg] = static_cast<int64_t>(blocks.size());
     const int64_t rows = h_track_off[n_seg];
     if (rows > 0 && !d_tracks) return ctx->fail("d_tracks is NULL");
     if (h_pt_off[n_seg] > 0 && !d_pts) return ctx->fail("d_pts is NULL");
@@ -583,21 +586,23 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     const int32_t nb = static_cast<int32_t>(blocks.size());
     SFM_CUDA(ctx, ctx->d_rblocks.reserve(blocks.size() + 1));
     SFM_CUDA(ctx, ctx->d_rcnt.reserve(static_cast<size_t>(rows) + 1));
-    SFM_CUDA(ctx, ctx->d_roff.reserve(static_cast<size_t>(rows) + 1));
+    SFM_CUDA(ctx, ctx->d_roff.reserve(2 * (blocks.size() + 1)));          // block offsets | block totals
     SFM_CUDA(ctx, ctx->d_rfirst.reserve(static_cast<size_t>(rows) * sfm::kRadiusKeep + 1));
     if (nb > 0)
         SFM_CUDA(ctx, ctx->ring.copy(ctx->d_rblocks.p, blocks.data(), sizeof(sfm::RadiusBlock) * blocks.size(), st));
-    if (rows > 0) SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_rcnt.p, 0, sizeof(long long) * rows, st));
     const double s_lim = radius_limit(threshold);
-    sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, rows, ctx->d_rcnt.p, ctx->d_rfirst.p,
-                             ctx->d_roff.p, st, &ctx->launches);
+    long long* d_block_off = ctx->d_roff.p;
+    long long* d_block_cnt = ctx->d_roff.p + nb + 1;
+    sfm::launch_radius_count(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_rcnt.p, ctx->d_rfirst.p,
+                             d_block_cnt, d_block_off, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
-    // match offsets at the segment boundaries: gathered on the device, n_seg + 1 words come back
+    // match offsets at the segment boundaries (a segment starts at a block boundary): gathered on
+    // the device, n_seg + 1 words come back
     const size_t n1 = static_cast<size_t>(n_seg) + 1;
     SFM_CUDA(ctx, ctx->d_meta.reserve(3 * n1));
     static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
-    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p, h_track_off, sizeof(int64_t) * n1, st));
-    sfm::launch_gather_offsets(ctx->d_roff.p, reinterpret_cast<const long long*>(ctx->d_meta.p),
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_meta.p, ctx->h_meta.data(), sizeof(int64_t) * n1, st));
+    sfm::launch_gather_offsets(d_block_off, reinterpret_cast<const long long*>(ctx->d_meta.p),
                                static_cast<int32_t>(n1), reinterpret_cast<long long*>(ctx->d_meta.p + n1), st,
                                &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
@@ -607,8 +612,8 @@ int sfm_radius_match(sfm_ctx* ctx, int32_t n_seg, const int64_t* h_track_off, co
     const int64_t total = h_seg_off[n_seg];
     if (total > cap) return 0;   // caller sees h_seg_off[n_seg] > cap and calls again with room
     // the fill pass writes global positions; segment-local positions follow from h_seg_off
-    sfm::launch_radius_fill(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_rfirst.p, ctx->d_roff.p, cap,
-                            d_out_track, d_out_pt, st, &ctx->launches);
+    sfm::launch_radius_fill(ctx->d_rblocks.p, nb, d_tracks, d_pts, s_lim, ctx->d_rcnt.p, ctx->d_rfirst.p,
+                            d_block_off, cap, d_out_track, d_out_pt, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     SFM_CUDA(ctx, cudaStreamSynchronize(st));
     return 0;

@@ -92,19 +92,20 @@ struct RadiusBlock {
     int32_t track0;    // index of row0 inside its segment
     int32_t pad;
 };
-// Counts per track row into d_row_cnt[n_rows] (+ the first kRadiusKeep point indices of each row
-// into d_first[n_rows * kRadiusKeep]), then their exclusive scan into d_row_off[n_rows + 1].
+// Counts per track row into d_row_cnt (+ the first kRadiusKeep point indices of each row into
+// d_first[row * kRadiusKeep]), block totals into d_block_cnt[n_blocks], then their exclusive scan
+// into d_block_off[n_blocks + 1].
 void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                         const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
-                         int32_t* d_first, long long* d_row_off, cudaStream_t st, int64_t* launches);
-// d_out[i] = d_row_off[d_at[i]]: the match offsets at the segment boundaries.
-void launch_gather_offsets(const long long* d_row_off, const long long* d_at, int32_t n, long long* d_out,
+                         const double* d_pts, double s_lim, long long* d_row_cnt, int32_t* d_first,
+                         long long* d_block_cnt, long long* d_block_off, cudaStream_t st, int64_t* launches);
+// d_out[i] = d_off[d_at[i]]: the match offsets at the segment boundaries.
+void launch_gather_offsets(const long long* d_off, const long long* d_at, int32_t n, long long* d_out,
                            cudaStream_t st, int64_t* launches);
 // (track index in its segment, point index in its segment) of every match, row-major per segment.
 void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                        const double* d_pts, double s_lim, const int32_t* d_first, const long long* d_row_off,
-                        long long cap, int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st,
-                        int64_t* launches);
+                        const double* d_pts, double s_lim, const long long* d_row_cnt, const int32_t* d_first,
+                        const long long* d_block_off, long long cap, int32_t* d_out_track, int32_t* d_out_pt,
+                        cudaStream_t st, int64_t* launches);
 
 // ---- ransac.cu
 void launch_gather_points(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,

@@ -7,7 +7,8 @@
 // for a whole batch of segments (one segment = the tracks x points of one image pair) at once.
 // The result is the list np.where yields: (track, point) index pairs in row-major order, per
 // segment.  Nothing is materialised but that list: a counting pass that also keeps the first
-// kRadiusKeep hits of every track, a scan of the per-track counts, and a fill pass that copies the
+// kRadiusKeep hits of every track and sums the counts per block, a scan of the block totals, and a
+// fill pass that scans its own tracks' counts on top of the block offset and copies the
 // kept hits to their place (a track matches a handful of points at most); only blocks that hold a
 // track with more hits than were kept repeat the comparison for those tracks.
 //
@@ -39,19 +40,34 @@ template <bool FILL>
 __global__ void __launch_bounds__(kRadiusRows)
 radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict__ tracks,
               const double2* __restrict__ pts, double s_lim, long long* __restrict__ row_cnt,
-              int32_t* __restrict__ first, const long long* __restrict__ row_off, long long cap,
-              int32_t* __restrict__ out_track, int32_t* __restrict__ out_pt) {
+              int32_t* __restrict__ first, long long* __restrict__ block_cnt,
+              const long long* __restrict__ block_off, long long cap, int32_t* __restrict__ out_track,
+              int32_t* __restrict__ out_pt) {
     __shared__ double2 tile[kRadiusTile];
+    __shared__ long long warp_tot[kRadiusRows / 32];
     const RadiusBlock b = blocks[blockIdx.x];
     const int local = static_cast<int>(threadIdx.x);
     const bool live = local < b.n_rows;
     const long long row = b.row0 + local;
     const double2 t = live ? tracks[row] : make_double2(0.0, 0.0);
     long long n = 0;
-    long long dst = (FILL && live) ? row_off[row] : 0;
+    long long dst = 0;
     bool scan = live;
     if (FILL) {
-        const long long cnt = live ? row_off[row + 1] - dst : 0;
+        // offsets of this block's tracks: exclusive scan of their counts on top of the block's offset
+        const long long cnt = live ? row_cnt[row] : 0;
+        const int lane = local & 31, warp = local >> 5;
+        long long x = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        long long before = block_off[blockIdx.x] + (x - cnt);
+        for (int w = 0; w < warp; ++w) before += warp_tot[w];
+        dst = before;
         scan = cnt > kRadiusKeep;
         if (!scan)
             for (int i = 0; i < static_cast<int>(cnt); ++i)
@@ -90,11 +106,25 @@ radius_kernel(const RadiusBlock* __restrict__ blocks, const double2* __restrict_
             }
         }
     }
-    if (!FILL && live) row_cnt[row] = n;
+    if (!FILL) {
+        if (live) row_cnt[row] = n;
+        // block total for the scan over blocks
+        long long x = n;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
+        __syncthreads();
+        if ((local & 31) == 0) warp_tot[local >> 5] = x;
+        __syncthreads();
+        if (local == 0) {
+            long long tot = 0;
+            for (int w = 0; w < kRadiusRows / 32; ++w) tot += warp_tot[w];
+            block_cnt[blockIdx.x] = tot;
+        }
+    }
 }
 
-// Exclusive scan of n counts into n + 1 offsets by one block (rows are few: a track list, not a
-// descriptor matrix); off[n] = total.
+// Exclusive scan of n block totals into n + 1 offsets by one block (one value per 256 tracks);
+// off[n] = total.
 constexpr int kScanThreads = 1024;
 
 __global__ void __launch_bounds__(kScanThreads) scan_kernel(const long long* __restrict__ cnt, long long n,
@@ -151,26 +181,27 @@ void launch_gather_offsets(const long long* d_row_off, const long long* d_at, in
 }
 
 void launch_radius_count(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                         const double* d_pts, double s_lim, long long n_rows, long long* d_row_cnt,
-                         int32_t* d_first, long long* d_row_off, cudaStream_t st, int64_t* launches) {
+                         const double* d_pts, double s_lim, long long* d_row_cnt, int32_t* d_first,
+                         long long* d_block_cnt, long long* d_block_off, cudaStream_t st, int64_t* launches) {
     if (n_blocks > 0) {
         radius_kernel<false><<<n_blocks, kRadiusRows, 0, st>>>(
             d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
-            d_row_cnt, d_first, nullptr, 0, nullptr, nullptr);
+            d_row_cnt, d_first, d_block_cnt, nullptr, 0, nullptr, nullptr);
         ++*launches;
     }
-    scan_kernel<<<1, kScanThreads, 0, st>>>(d_row_cnt, n_rows, d_row_off);
+    scan_kernel<<<1, kScanThreads, 0, st>>>(d_block_cnt, n_blocks, d_block_off);
     ++*launches;
 }
 
 void launch_radius_fill(const RadiusBlock* d_blocks, int32_t n_blocks, const double* d_tracks,
-                        const double* d_pts, double s_lim, const int32_t* d_first, const long long* d_row_off,
-                        long long cap, int32_t* d_out_track, int32_t* d_out_pt, cudaStream_t st,
-                        int64_t* launches) {
+                        const double* d_pts, double s_lim, const long long* d_row_cnt, const int32_t* d_first,
+                        const long long* d_block_off, long long cap, int32_t* d_out_track, int32_t* d_out_pt,
+                        cudaStream_t st, int64_t* launches) {
     if (n_blocks <= 0) return;
     radius_kernel<true><<<n_blocks, kRadiusRows, 0, st>>>(
         d_blocks, reinterpret_cast<const double2*>(d_tracks), reinterpret_cast<const double2*>(d_pts), s_lim,
-        nullptr, const_cast<int32_t*>(d_first), d_row_off, cap, d_out_track, d_out_pt);
+        const_cast<long long*>(d_row_cnt), const_cast<int32_t*>(d_first), nullptr, d_block_off, cap, d_out_track,
+        d_out_pt);
     ++*launches;
 }
 
