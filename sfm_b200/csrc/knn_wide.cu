@@ -199,36 +199,60 @@ __device__ __forceinline__ int key_col(uint32_t key, const KeyFmt& kf, int colba
     return (idx >> 3) * kTileN + colbase + (idx & 7) * kUnit;
 }
 
-// Exact top-2 of the (at most) two parked units, visited in ascending column order.
+// Exact top-2 of the (at most) two parked units, branch-free.  The 32 parked accumulators become
+// packed candidates  x = (2v + 2 - parity) << 5 | (31 - idx)  with idx = 0..15 for the unit with the
+// lower columns and 16..31 for the other one: 2v - parity orders like the exact key (it is the key
+// plus 2C), the tag makes the lowest column win among equal keys (OpenCV's rule), invalid candidates
+// are 0 and every valid one is >= 32.  Two running maxima (3 min/max per candidate) replace the
+// divergent insertion of one candidate at a time.
+__device__ __forceinline__ void resolve_pass(uint32_t& m1, uint32_t& m2, int c, uint32_t src,
+                                             const int32_t* __restrict__ nbase, int t_cnt, int unit) {
+    if (c < 0) return;
+    uint4 q[kUnit / 4];
+    int4 nb[kUnit / 4];
+#pragma unroll
+    for (int g = 0; g < kUnit / 4; ++g) {
+        q[g] = lds128(src + g * kSlotRow);
+        nb[g] = __ldg(reinterpret_cast<const int4*>(nbase + c) + g);
+    }
+    const bool whole = c + kUnit <= t_cnt;      // only the last unit of an image can be partial
+#pragma unroll
+    for (int g = 0; g < kUnit / 4; ++g) {
+        const uint32_t vv[4] = {q[g].x, q[g].y, q[g].z, q[g].w};
+        const int nn[4] = {nb[g].x, nb[g].y, nb[g].z, nb[g].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const uint32_t tag = 64u + 31u - static_cast<uint32_t>(unit * kUnit + 4 * g + e);
+            uint32_t x = vv[e] * 64u + tag - 32u * static_cast<uint32_t>(nn[e] & 1);
+            if (!whole && c + 4 * g + e >= t_cnt) x = 0;
+            m2 = max(m2, min(m1, x));
+            m1 = max(m1, x);
+        }
+    }
+}
+
 __device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const KeyFmt& kf, int colbase,
                                                uint32_t slots, const int32_t* __restrict__ nbase, int t_cnt) {
-    Top2K r{INT_MIN, INT_MIN, -1, -1};
     const int s1 = s.k1 & 1, s2 = s.k2 & 1;
     const int c1 = n_seen >= 1 ? key_col(s.k1, kf, colbase) : -1;
     const int c2 = n_seen >= 2 ? key_col(s.k2, kf, colbase) : -1;
     const bool second_first = c2 >= 0 && c2 < c1;
-    // both neighbours of this thread's columns have v >= the second unit maximum (a lower bound of
-    // it when the key holds a truncated maximum): everything below is skipped without forming a key
-    const int vmin = n_seen >= 2 ? static_cast<int>((s.k2 >> (kf.ubits + 1)) << kf.sh) : 0;
-#pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-        const bool take2 = (pass == 0) == second_first;
-        const int c = take2 ? c2 : c1;
-        if (c < 0) continue;
-        const uint32_t src = slots + (take2 ? s2 : s1) * kSlotStride;
-#pragma unroll
-        for (int g = 0; g < kUnit / 4; ++g) {
-            const uint4 q = lds128(src + g * kSlotRow);
-            const int4 nb = __ldg(reinterpret_cast<const int4*>(nbase + c) + g);
-            const int vv[4] = {static_cast<int>(q.x), static_cast<int>(q.y), static_cast<int>(q.z),
-                               static_cast<int>(q.w)};
-            const int pp[4] = {nb.x & 1, nb.y & 1, nb.z & 1, nb.w & 1};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int col = c + 4 * g + e;
-                if (col < t_cnt && vv[e] >= vmin) top2k_insert(r, 2 * vv[e] - (pp[e] + 2 * kFoldC), col);
-            }
-        }
+    const int ca = second_first ? c2 : c1, cb = second_first ? c1 : c2;
+    const uint32_t sa = slots + (second_first ? s2 : s1) * kSlotStride;
+    const uint32_t sb = slots + (second_first ? s1 : s2) * kSlotStride;
+    uint32_t m1 = 0, m2 = 0;
+    resolve_pass(m1, m2, ca, sa, nbase, t_cnt, 0);
+    resolve_pass(m1, m2, cb, sb, nbase, t_cnt, 1);
+    Top2K r{INT_MIN, INT_MIN, -1, -1};
+    if (m1) {
+        const int idx = 31 - static_cast<int>(m1 & 31u);
+        r.k1 = static_cast<int>(m1 >> 5) - 2 - 2 * kFoldC;
+        r.i1 = idx < kUnit ? ca + idx : cb + idx - kUnit;
+    }
+    if (m2) {
+        const int idx = 31 - static_cast<int>(m2 & 31u);
+        r.k2 = static_cast<int>(m2 >> 5) - 2 - 2 * kFoldC;
+        r.i2 = idx < kUnit ? ca + idx : cb + idx - kUnit;
     }
     return r;
 }
