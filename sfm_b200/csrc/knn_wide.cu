@@ -205,26 +205,33 @@ __device__ __forceinline__ int key_col(uint32_t key, const KeyFmt& kf, int colba
 // plus 2C), the tag makes the lowest column win among equal keys (OpenCV's rule), invalid candidates
 // are 0 and every valid one is >= 32.  Two running maxima (3 min/max per candidate) replace the
 // divergent insertion of one candidate at a time.
-__device__ __forceinline__ void resolve_pass(uint32_t& m1, uint32_t& m2, int c, uint32_t src,
-                                             const int32_t* __restrict__ nbase, int t_cnt, int unit) {
-    if (c < 0) return;
+struct ParkedUnit {
     uint4 q[kUnit / 4];
     int4 nb[kUnit / 4];
+};
+
+// c < 0 (fewer than two units seen: tiny train images) reads unit 0 and masks everything.
+__device__ __forceinline__ void resolve_load(ParkedUnit& u, int c, uint32_t src, const int32_t* __restrict__ nbase) {
+    const int cc = max(c, 0);
 #pragma unroll
     for (int g = 0; g < kUnit / 4; ++g) {
-        q[g] = lds128(src + g * kSlotRow);
-        nb[g] = __ldg(reinterpret_cast<const int4*>(nbase + c) + g);
+        u.nb[g] = __ldg(reinterpret_cast<const int4*>(nbase + cc) + g);
+        u.q[g] = lds128(src + g * kSlotRow);
     }
-    const bool whole = c + kUnit <= t_cnt;      // only the last unit of an image can be partial
+}
+
+__device__ __forceinline__ void resolve_pass(uint32_t& m1, uint32_t& m2, const ParkedUnit& u, int c, int t_cnt,
+                                             int unit) {
+    const int n_ok = c < 0 ? 0 : t_cnt - c;     // valid columns of the unit (>= 16 unless it is the last one)
 #pragma unroll
     for (int g = 0; g < kUnit / 4; ++g) {
-        const uint32_t vv[4] = {q[g].x, q[g].y, q[g].z, q[g].w};
-        const int nn[4] = {nb[g].x, nb[g].y, nb[g].z, nb[g].w};
+        const uint32_t vv[4] = {u.q[g].x, u.q[g].y, u.q[g].z, u.q[g].w};
+        const int nn[4] = {u.nb[g].x, u.nb[g].y, u.nb[g].z, u.nb[g].w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             const uint32_t tag = 64u + 31u - static_cast<uint32_t>(unit * kUnit + 4 * g + e);
             uint32_t x = vv[e] * 64u + tag - 32u * static_cast<uint32_t>(nn[e] & 1);
-            if (!whole && c + 4 * g + e >= t_cnt) x = 0;
+            if (n_ok < kUnit && 4 * g + e >= n_ok) x = 0;
             m2 = max(m2, min(m1, x));
             m1 = max(m1, x);
         }
@@ -240,9 +247,13 @@ __device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const K
     const int ca = second_first ? c2 : c1, cb = second_first ? c1 : c2;
     const uint32_t sa = slots + (second_first ? s2 : s1) * kSlotStride;
     const uint32_t sb = slots + (second_first ? s1 : s2) * kSlotStride;
+    // all sixteen loads first: the norm rows come from L2, one latency for both units
+    ParkedUnit ua, ub;
+    resolve_load(ua, ca, sa, nbase);
+    resolve_load(ub, cb, sb, nbase);
     uint32_t m1 = 0, m2 = 0;
-    resolve_pass(m1, m2, ca, sa, nbase, t_cnt, 0);
-    resolve_pass(m1, m2, cb, sb, nbase, t_cnt, 1);
+    resolve_pass(m1, m2, ua, ca, t_cnt, 0);
+    resolve_pass(m1, m2, ub, cb, t_cnt, 1);
     Top2K r{INT_MIN, INT_MIN, -1, -1};
     if (m1) {
         const int idx = 31 - static_cast<int>(m1 & 31u);
