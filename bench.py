@@ -392,6 +392,9 @@ def main():
     ap.add_argument("--mutual", type=int, default=0, help="1: add the mutual-NN check (second, reversed kNN pass)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    args.steps = max(1, args.steps)
+    if args.impl != "reference":
+        args.warmup = max(3, args.warmup)     # timing rule: at least three warm-up steps; the line reports what ran
     if args.impl == "reference":
         run_reference(args)
     else:
