@@ -36,8 +36,6 @@ OPS_PER_CMP = 256.0                 # 2 * 128 int8 ops per descriptor comparison
 
 
 def workload(n_gpus: int):
-    if n_gpus <= 1:
-        return dict(name="synthetic 36 images x 8192 SIFT descriptors, exhaustive 630 pairs", n_images=36)
     return dict(name="synthetic 200 images x 8192 SIFT descriptors, exhaustive 19900 pairs", n_images=200)
 
 

@@ -235,6 +235,16 @@ SFM_API int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image
  * a.b + 2016029 - floor(||b||^2 / 2) for query rows q_row.. against descriptor rows t_row..,
  * written to d_out i32 [128,256]. */
 SFM_API int sfm_debug_wide_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+/* Debug: the same folded accumulators for a 128 x 128 tile through the TS path
+ * (sfm_b200/csrc/knn_ts.cu: query rows written to tensor memory with tcgen05.st, tcgen05.mma with
+ * the A operand in TMEM), written to d_out i32 [128,128]. */
+SFM_API int sfm_debug_ts_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+/* Issue-rate probe of 128 x tile_n x 32 u8 MMAs (tile_n = 64, 96, 128, 192 or 256) in groups of
+ * five, accumulators rotating over 384 / tile_n TMEM stages, no data movement.  ts != 0: A operand
+ * in tensor memory, else in shared memory; commit != 0: one tcgen05.commit per group.
+ * *ms = elapsed (CUDA events), *ops = int8 operations issued. */
+SFM_API int sfm_debug_ts_rate_probe(sfm_ctx* ctx, int32_t groups, int32_t tile_n, int32_t ts, int32_t commit,
+                            float* ms, double* ops, void* stream);
 /* TMEM read-rate probe: every SM runs `warps` warps issuing `iters` tcgen05.ld each
  * (variant 0: 32x32b.x32 + wait each; 1: .x32, wait every 4; 2: .x64 + wait each;
  * 3: 16x256b.x8, wait every 4); *h_cycles = slowest warp's SM cycles (synchronises). */

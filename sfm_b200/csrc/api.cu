@@ -108,9 +108,10 @@ struct sfm_ctx {
     bool have_tmap = false;
     DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
+    DevBuf<uint32_t> d_par_bits;   // norm parities of the padded column space, 32 per word (knn_ts.cu)
     DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
-    int knn_auto = 5;            // what mode 0 resolves to: 0 = knn.cu fold + generic, 5 = wide fold + generic
+    int knn_auto = 8;            // what mode 0 resolves to: 8 = TS kernel + generic, 5 = wide fold + generic
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
@@ -262,6 +263,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_flags.release();
     ctx->d_bias.release();
     ctx->d_bias32.release();
+    ctx->d_par_bits.release();
     ctx->d_fix_list.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
@@ -322,6 +324,7 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     SFM_CUDA(ctx, ctx->d_bias.reserve(static_cast<size_t>(x_rows) * SFM_DESC_DIM));
     SFM_CUDA(ctx, ctx->d_bias32.reserve(static_cast<size_t>(total + SFM_TTILE) * 32));
     SFM_CUDA(ctx, ctx->d_fix_list.reserve(2 * static_cast<size_t>(sfm_ctx::kFixCap)));
+    SFM_CUDA(ctx, ctx->d_par_bits.reserve(static_cast<size_t>(ctx->pad_total) / 32 + 4));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_x_off.p, ctx->h_x.data(), sizeof(int64_t) * (n_images + 1),
                                   cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
@@ -363,6 +366,7 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, ctx->d_x_off.p, n_images,
                       ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_bias.p, ctx->d_flags.p, st, &ctx->launches);
     sfm::launch_bias32(ctx->d_norms.p, total, ctx->d_bias32.p, ctx->d_flags.p, st, &ctx->launches);
+    sfm::launch_parity_bits(ctx->d_norms_pad.p, ctx->pad_total, ctx->d_par_bits.p, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     return 0;
 }
@@ -394,20 +398,27 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
     sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
                            ctx->d_x_off.p, ctx->d_work.p, st, &ctx->launches);
-    // knn_mode 0: wide folded kernel, or the generic one when a norm is beyond the fold range (both are
+    // knn_mode 0: the TS kernel (knn_ts.cu), or the generic one when a norm is beyond the fold range (both are
     // launched; the one that does not apply exits at its first instruction).  1: generic, 2-4: N = 128
-    // folded kernel and its probes (knn.cu), 5: wide only, 6/7: wide timing probes.
+    // folded kernel and its probes (knn.cu), 5: wide kernel only (knn_wide.cu), 6/7: its timing probes,
+    // 8: TS kernel only, 10/11: its timing probes.
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
-    if (km >= 5)
+    const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
+    if (km >= 8)
+        r = sfm::launch_knn2_ts(ctx->tmap, ctx->tmap_ax32, ctx->d_desc, ctx->d_bias32.p, ctx->d_work.p, n_work,
+                                ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
+                                km == 10 ? 1 : (km == 11 ? 2 : 0), ctx->knn_mode != 0, ctx->knn_tuning,
+                                ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches);
+    else if (km >= 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
-                                  ctx->knn_tuning, ctx->d_fix_list.p,
-                                  (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap, d_knn,
+                                  ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
                                   ctx->num_sms, st, &ctx->launches);
-    if (!r && km <= 5 && !(km == 5 && ctx->knn_mode != 0))
+    const bool folded_auto = (km == 5 || km == 8) && ctx->knn_mode == 0;
+    if (!r && (km < 5 || folded_auto))
         r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
-                             ctx->d_norms_pad.p, ctx->d_flags.p, km == 5 ? 9 : km, ctx->knn_tuning, d_knn,
+                             ctx->d_norms_pad.p, ctx->d_flags.p, folded_auto ? 9 : km, ctx->knn_tuning, d_knn,
                              ctx->num_sms, st, &ctx->launches);
     if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     return 0;
@@ -693,6 +704,47 @@ int sfm_debug_wide_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_o
     return 0;
 }
 
+int sfm_debug_ts_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream) {
+    if (!ctx) return 1;
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
+    if (!d_out) return ctx->fail("d_out is NULL");
+    if (q_row < 0 || t_row < 0 || q_row + 128 > ctx->total_rows || t_row >= ctx->total_rows)
+        return ctx->fail("tile rows out of range");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    int r = sfm::launch_debug_ts(ctx->tmap, ctx->tmap_ax32, ctx->d_desc, ctx->d_bias32.p, static_cast<int32_t>(q_row),
+                                 static_cast<int32_t>(t_row), d_out, static_cast<cudaStream_t>(stream),
+                                 &ctx->launches);
+    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_debug_ts_rate_probe(sfm_ctx* ctx, int32_t groups, int32_t tile_n, int32_t ts, int32_t commit, float* ms,
+                            double* ops, void* stream) {
+    if (!ctx) return 1;
+    if (groups < 1 || !ms || !ops) return ctx->fail("bad probe arguments");
+    if (tile_n != 64 && tile_n != 96 && tile_n != 128 && tile_n != 192 && tile_n != 256)
+        return ctx->fail("tile_n must be 64, 96, 128, 192 or 256");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1;
+    SFM_CUDA(ctx, cudaEventCreate(&e0));
+    SFM_CUDA(ctx, cudaEventCreate(&e1));
+    int r = sfm::launch_ts_rate_probe(groups, tile_n, ts, commit, ctx->num_sms, st, &ctx->launches);   // warm-up
+    if (!r) {
+        cudaEventRecord(e0, st);
+        r = sfm::launch_ts_rate_probe(groups, tile_n, ts, commit, ctx->num_sms, st, &ctx->launches);
+        cudaEventRecord(e1, st);
+    }
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (!r && e == cudaSuccess) cudaEventElapsedTime(ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (r || e != cudaSuccess)
+        return ctx->fail("probe failed: %s", cudaGetErrorString(r ? static_cast<cudaError_t>(r) : e));
+    *ops = 2.0 * 128.0 * tile_n * 32.0 * 5.0 * static_cast<double>(groups) * ctx->num_sms;
+    return 0;
+}
+
 int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant, int32_t iters, int64_t* h_cycles,
                             void* stream) {
     if (!ctx) return 1;
@@ -742,7 +794,7 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (mode < 0 || mode > 7) return ctx->fail("knn mode must be 0..7");
+    if (mode < 0 || mode > 11 || mode == 9) return ctx->fail("knn mode must be 0..8, 10 or 11");
     ctx->knn_mode = mode;
     return 0;
 }

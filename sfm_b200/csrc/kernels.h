@@ -55,6 +55,26 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                       int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches);
 
+// ---- knn_ts.cu (A operand in TMEM; probes and debug tile)
+int launch_debug_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_ax, const uint8_t* d_desc,
+                    const uint8_t* d_bias32, int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st,
+                    int64_t* launches);
+// Fix-up pass shared by the folded kernels (knn_wide.cu): rows flagged kFlagged are recomputed by brute force.
+int launch_knn_fix(const WorkItem* d_work, int64_t n_work, const uint8_t* d_desc, const int32_t* d_norms,
+                   const int32_t* d_flags, const int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms,
+                   cudaStream_t st, int64_t* launches);
+// Norm parities of the padded column space as a bitmap (32 columns per word).
+void launch_parity_bits(const int32_t* d_norms_pad, int64_t pad_total, uint32_t* d_par_bits, cudaStream_t st,
+                        int64_t* launches);
+// TS kNN kernel: tmap = descriptor rows (128-row boxes), tmap_x = fold operand rows (32 B, 128-row boxes).
+int launch_knn2_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc, const uint8_t* d_bias32,
+                   const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
+                   const uint32_t* d_par_bits, int32_t* d_flags, int variant, int force, const struct KnnTuning& tn,
+                   int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st,
+                   int64_t* launches);
+int launch_ts_rate_probe(int groups, int tile_n, int ts, int commit, int num_sms, cudaStream_t st,
+                         int64_t* launches);
+
 // ---- probes.cu
 int launch_tmem_ld_probe(int warps, int variant, int iters, int num_sms, long long* d_out, cudaStream_t st,
                          int64_t* launches);

@@ -892,6 +892,16 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
     return static_cast<int>(e);
 }
 
+int launch_knn_fix(const WorkItem* d_work, int64_t n_work, const uint8_t* d_desc, const int32_t* d_norms,
+                   const int32_t* d_flags, const int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms,
+                   cudaStream_t st, int64_t* launches) {
+    knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_flags,
+                                                      reinterpret_cast<const int2*>(d_fix_list), fix_cap,
+                                                      reinterpret_cast<int4*>(d_knn));
+    ++*launches;
+    return static_cast<int>(cudaGetLastError());
+}
+
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                       int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches) {
     const size_t smem = kATileBytes + kBTileBytes + kXTileBytes + kAxBytes + 64 + 1024;

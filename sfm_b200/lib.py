@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_ts_rate_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -93,6 +93,8 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_probe_int8_rate.argtypes = [vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_fold_tile.argtypes = [vp, i64, i32, i32, vp, vp]
     lib.sfm_debug_wide_tile.argtypes = [vp, i64, i64, vp, vp]
+    lib.sfm_debug_ts_tile.argtypes = [vp, i64, i64, vp, vp]
+    lib.sfm_debug_ts_rate_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_set_knn_mode.argtypes = [vp, i32]
     lib.sfm_debug_set_knn_waits.argtypes = [vp, i32, i32]
     lib.sfm_debug_mma_handshake_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), vp]
@@ -375,6 +377,19 @@ class Context:
         self._check(self.lib.sfm_debug_wide_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
                                                  self._stream()))
         return out
+
+    def debug_ts_tile(self, q_row, t_row):
+        out = self.empty((128, 128), self.torch.int32)
+        self._check(self.lib.sfm_debug_ts_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
+                                               self._stream()))
+        return out
+
+    def ts_rate_probe(self, tile_n, ts=1, commit=0, groups=8192):
+        """-> TOP/s of groups of five 128 x tile_n x 32 u8 MMAs (A in TMEM when ts, else shared memory)."""
+        ms, ops = C.c_float(), C.c_double()
+        self._check(self.lib.sfm_debug_ts_rate_probe(self.h, groups, tile_n, int(ts), int(commit), C.byref(ms),
+                                                     C.byref(ops), self._stream()))
+        return ops.value / (ms.value * 1e-3) / 1e12
 
     def tmem_ld_probe(self, warps, variant, iters=4096):
         """-> bytes of TMEM read per cycle per SM for the given warp count / load shape."""

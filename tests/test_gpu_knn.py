@@ -233,9 +233,26 @@ def test_wide_fold_tile_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
-def test_knn_wide_fixup_paths(ctx):
-    """Data made of few distinct descriptors: unit maxima tie everywhere, so the wide kernel's
-    tied-unit recompute and its brute-force fix-up pass (list driven, and the overflow scan with the
+def test_ts_fold_tile_accumulators(ctx):
+    """TS path (query rows written to tensor memory with tcgen05.st, tcgen05.mma with the A operand in
+    TMEM, N = 128): accumulators of a 128 x 128 tile must equal a.b + C - (||b||^2 >> 1) exactly."""
+    descs = _sift_like([300, 1500, 700], 31)
+    off = register(ctx, descs)
+    total = int(off[-1])
+    allrows = np.concatenate(descs).astype(np.int64)
+    for q_row, t_row in [(0, 300), (100, 300 + 512), (1800 + 131, 300 + 1024), (300 + 640, 1800), (7, 0),
+                         (total - 128, total - 100)]:
+        got = ctx.debug_ts_tile(q_row, t_row).cpu().numpy()
+        a = allrows[q_row:q_row + 128]
+        b = allrows[t_row:t_row + 128]
+        want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
+        assert np.array_equal(got[:len(a), :len(b)], want)
+
+
+@pytest.mark.parametrize("mode", [5, 8])
+def test_knn_fixup_paths(ctx, mode):
+    """Data made of few distinct descriptors: unit maxima tie everywhere, so the folded kernels'
+    tied-unit recompute and their brute-force fix-up pass (list driven, and the overflow scan with the
     list shrunk to 4 entries) produce the rows; all must equal the oracle incl. the tie rule."""
     rng = np.random.default_rng(77)
     base = _sift_like([6], 41)[0]
@@ -243,7 +260,7 @@ def test_knn_wide_fixup_paths(ctx):
     register(ctx, descs)
     pairs = [(0, 1), (1, 2), (2, 0), (1, 0)]
     for pf in (0, 8):
-        ctx.set_knn_mode(5)
+        ctx.set_knn_mode(mode)
         ctx.set_knn_probe_flags(pf)
         try:
             before = ctx.brute_rows()
@@ -256,13 +273,15 @@ def test_knn_wide_fixup_paths(ctx):
             check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-def test_knn_wide_long_train_images(ctx):
-    """Wide kernel with train images beyond 8192 rows: unit ids need more than 8 key bits, the unit
-    maxima are truncated in the packed keys and ties on the truncated value are recomputed."""
+@pytest.mark.parametrize("mode", [5, 8])
+def test_knn_long_train_images(ctx, mode):
+    """Folded kernels with long train images (wide: beyond 8192 rows, TS: beyond 16384): unit ids need
+    more than 8 key bits, the unit maxima are truncated in the packed keys and ties on the truncated
+    value are recomputed."""
     sizes = [700, 9000, 20000]
     descs = _sift_like(sizes, 35)
     register(ctx, descs)
-    ctx.set_knn_mode(5)
+    ctx.set_knn_mode(mode)
     try:
         pairs = [(0, 1), (0, 2), (1, 2)]
         got, ro = gpu_knn(ctx, pairs)
@@ -272,10 +291,10 @@ def test_knn_wide_long_train_images(ctx):
         check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-@pytest.mark.parametrize("mode", [1, 2, 5])
+@pytest.mark.parametrize("mode", [1, 2, 5, 8])
 def test_knn_variants_match_oracle(ctx, mode):
-    """Generic (1), N = 128 folded (2) and wide folded (5) kernels, forced, on SIFT-like data with
-    partial tiles and ties."""
+    """Generic (1), N = 128 folded (2), wide folded (5) and TS (8) kernels, forced, on SIFT-like data
+    with partial tiles and ties."""
     sizes = [1, 2, 5, 127, 128, 129, 255, 256, 257, 383, 512, 513, 640, 1025, 2000]
     descs = _sift_like(sizes, 32)
     register(ctx, descs)
