@@ -5,18 +5,26 @@ pairs/s and descriptor comparisons/s as int8 TOPS vs peak).
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
 
 A step is one pass of the hot path (kNN k=2 -> ratio -> RANSAC F -> verification
--> result packing) over every pair of a synthetic SIFT-like image set:
-  N = 1   36 images x 8192 descriptors, 630 pairs   (BASELINE configs[1])
-  N > 1   200 images x 8192 descriptors, 19,900 pairs partitioned over the ranks
-          (BASELINE configs[2]); descriptors replicated with one NCCL all-gather.
+-> result packing) over every pair of a synthetic SIFT-like image set.  The SAME
+workload runs at every N -- BASELINE configs[2], 200 images x 8192 descriptors,
+19,900 pairs, partitioned over the ranks -- so values at N = 1, 2, 4, 8 are one
+strong-scaling series.  The set is generated on the host with numpy's default_rng,
+image i from (seed, 1 + i): the CPU arm, the CUDA arm and every rank see identical
+bytes (each rank generates its own image block, one NCCL all-gather replicates it).
+
 `value` is device-resident throughput (CUDA events, max over ranks); `e2e` goes
 through the public engine call with host buffers (H2D + D2H inside the timed
-region).  `--impl reference` times the reference's own OpenCV CPU path (via the
-oracle, which restates the reference's cv2 calls) on the host cores.
+region).  `stages_ms` splits one step into its kernels, `parity_check` runs a sample
+of the TIMED set through the oracle (untimed), `target_config` adds one timed step
+of the configurations the north-star target is quoted on (1000 x 8k; 500 x 32k at
+8 GPUs).  `--impl reference` times the reference's own OpenCV CPU path (via the
+oracle, which restates the reference's cv2 calls) on the host cores, on pairs
+sampled from the same arrays.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -30,17 +38,39 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-N_DESC = 8192
 NOMINAL_INT8_TOPS = 4500.0          # B200 dense int8 datasheet figure
 OPS_PER_CMP = 256.0                 # 2 * 128 int8 ops per descriptor comparison
+RATIO = 0.75
+TIE_FRAC = 0.01
+
+WORKLOADS = {                        # BASELINE.json configs[1..4]; seeds = base + config index
+    "36x8k": dict(n_images=36, n_desc=8192, seed_off=1),
+    "200x8k": dict(n_images=200, n_desc=8192, seed_off=2),
+    "1000x8k": dict(n_images=1000, n_desc=8192, seed_off=3),
+    "500x32k": dict(n_images=500, n_desc=32768, seed_off=4),
+}
 
 
-def workload(n_gpus: int):
-    return dict(name="synthetic 200 images x 8192 SIFT descriptors, exhaustive 19900 pairs", n_images=200)
+def workload(key: str):
+    w = dict(WORKLOADS[key])
+    n = w["n_images"]
+    w["key"] = key
+    w["pairs"] = n * (n - 1) // 2
+    w["name"] = f"synthetic {n} images x {w['n_desc']} SIFT descriptors, exhaustive {w['pairs']} pairs"
+    return w
+
+
+def config_of(wl, mutual):
+    """The `config` object: identical in the B200 arm and the reference arm."""
+    from sfm_b200 import synth
+    return {"workload": wl["name"], "n_images": wl["n_images"], "n_desc": wl["n_desc"], "pairs": wl["pairs"],
+            "ratio": RATIO, "mutual_nn": bool(mutual), "seed": synth.BASE_SEED + wl["seed_off"],
+            "tie_frac": TIE_FRAC, "generator": "numpy default_rng on the host, image i from (seed, 1 + i)"}
 
 
 def all_pairs(n):
-    return np.array([(i, j) for i in range(n) for j in range(i + 1, n)], np.int32)
+    iu = np.triu_indices(n, 1)
+    return np.ascontiguousarray(np.stack(iu, 1).astype(np.int32))
 
 
 # --------------------------------------------------------------------- clocks
@@ -72,17 +102,6 @@ class ClockSampler:
     def mark(self):
         """Samples before this point (sampler start-up, warm-up) are not part of the summary."""
         self.rows = self.rows[len(self.rows):]
-        self.t_mark = time.perf_counter()
-
-    def extend_until(self, n_samples: int, load, limit_s: float = 6.0):
-        """nvidia-smi needs a moment to start (longer with 8 pollers on one box): if the timed region
-        was shorter than that, keep the same load running, untimed, until n_samples rows exist."""
-        t0 = time.perf_counter()
-        extended = False
-        while self.proc and len(self.rows) < n_samples and time.perf_counter() - t0 < limit_s:
-            load()
-            extended = True
-        return extended
 
     def __exit__(self, *a):
         if self.proc:
@@ -112,81 +131,115 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------- CPU reference arm
-def cpu_reference_sample(desc, kps, offsets, pairs, budget_s: float, max_pairs: int):
+def cpu_pairs(images, sample, mutual=False):
     """The reference's OpenCV path (BFMatcher.knnMatch + ratio loop + findFundamentalMat +
-    geometric_verification + verify_match_quality; utils/find_matches.py:141-214,
-    :272-290) on a bounded sample of the workload's pairs.  Returns (pairs_done, seconds, cores)."""
-    import cv2
+    geometric_verification + verify_match_quality; utils/find_matches.py:141-214, :272-290) over
+    `sample` = [(i, j)], images = {i: (desc, kps)}.  Returns seconds."""
     from oracle import pipeline as opipe
-    cores = os.cpu_count() or 1
-    cv2.setNumThreads(cores)
-    rng = np.random.default_rng(20240)
-    order = rng.permutation(len(pairs))[:max_pairs]
     t0 = time.perf_counter()
-    done = 0
-    for k in order:
-        i, j = pairs[k]
-        a, b = slice(offsets[i], offsets[i + 1]), slice(offsets[j], offsets[j + 1])
-        opipe.process_pair(desc[a], kps[a], desc[b], kps[b], mutual=False, use_cv2=True)
-        done += 1
-        if time.perf_counter() - t0 > budget_s:
-            break
-    return done, time.perf_counter() - t0, min(cores, cv2.getNumThreads())
+    for i, j in sample:
+        (d1, k1), (d2, k2) = images[int(i)], images[int(j)]
+        opipe.process_pair(d1, k1, d2, k2, mutual=mutual, use_cv2=True)
+    return time.perf_counter() - t0
+
+
+def sample_pairs(wl, n_sample, seed=7):
+    pairs = all_pairs(wl["n_images"])
+    order = np.random.default_rng(seed).permutation(len(pairs))[:n_sample]
+    return pairs[np.sort(order)]
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on the host cores."""
+    """--impl reference: the reference's CPU implementation of the path on the host cores, on pairs
+    sampled (seeded) from the SAME arrays the B200 arm matches."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-    from sfm_b200 import synth
-    wl = workload(args.gpus)
-    n = wl["n_images"]
-    # the same synthetic set as the B200 arm (seeded), generated on the CPU for a sample of images
-    n_gen = min(n, 12)
-    s = synth.make_image_set(n_gen, N_DESC, seed=synth.BASE_SEED + (1 if n == 36 else 2), tie_frac=0.01)
-    desc, kps, off = s.desc.numpy(), s.kps.numpy(), s.offsets.numpy()
-    pairs = all_pairs(n_gen)
-    per_step = max(2, min(8, len(pairs) // max(1, args.steps + args.warmup)))
-    rng = np.random.default_rng(7)
-    order = rng.permutation(len(pairs))
     import cv2
-    from oracle import pipeline as opipe
+    from sfm_b200 import synth
+    wl = workload(args.workload)
     cores = os.cpu_count() or 1
     cv2.setNumThreads(cores)
+    n_steps = args.steps + args.warmup
+    per_step = min(16, max(2, -(-64 // max(args.steps, 1))))      # >= 64 pairs over the timed steps
+    samp = sample_pairs(wl, per_step * n_steps)
+    sc = synth.make_scene(wl["n_images"], wl["n_desc"], synth.BASE_SEED + wl["seed_off"], tie_frac=TIE_FRAC)
+    ids = sorted(set(int(x) for x in samp.ravel()))
+    images = dict(zip(ids, synth.make_images(sc, ids)))        # untimed: synthetic inputs
 
     def step(k):
-        for idx in order[(k * per_step) % len(order):][:per_step]:
-            i, j = pairs[idx]
-            a, b = slice(off[i], off[i + 1]), slice(off[j], off[j + 1])
-            opipe.process_pair(desc[a], kps[a], desc[b], kps[b], mutual=False, use_cv2=True)
+        return cpu_pairs(images, samp[k * per_step:(k + 1) * per_step], mutual=bool(args.mutual))
 
     for k in range(args.warmup):
         step(k)
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        step(args.warmup + k)
-    dt = time.perf_counter() - t0
-    pairs_s = per_step * args.steps / dt
-    cmp_s = pairs_s * N_DESC * N_DESC
+    dt = sum(step(args.warmup + k) for k in range(args.steps))
+    done = per_step * args.steps
+    pairs_s = done / dt
+    cmp_s = pairs_s * wl["n_desc"] * wl["n_desc"]
     line = {
         "impl": "reference", "metric": "image_pairs_per_sec", "value": pairs_s, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "mutual_nn": False, "ratio": 0.75,
-                   "note": f"each step = {per_step} pairs sampled from the workload (bounded CPU sample)"},
+        "config": config_of(wl, args.mutual),
         "comparisons_per_sec": cmp_s, "int8_equiv_tops": cmp_s * OPS_PER_CMP / 1e12,
         "cpu_baseline": {"value": pairs_s, "unit": "pairs/s", "cores": min(cores, cv2.getNumThreads()),
                          "kind": "port",
-                         "sample": f"{per_step * args.steps} pairs of 8192x8192 descriptors through the reference's own "
-                                   f"OpenCV calls (cv2 {cv2.__version__} BFMatcher.knnMatch + ratio loop + findFundamentalMat "
-                                   "+ geometric_verification), restated by oracle/pipeline.py"},
+                         "sample": f"{done} pairs ({per_step} per step) drawn with a fixed seed from the workload's "
+                                   f"{wl['pairs']} pairs, same arrays as the B200 arm, through the reference's own "
+                                   f"OpenCV calls (cv2 {cv2.__version__} BFMatcher.knnMatch + ratio loop + "
+                                   "findFundamentalMat + geometric_verification), restated by oracle/pipeline.py; "
+                                   "pairs/s extrapolates linearly (every pair is the same n_desc x n_desc comparisons)"},
         "e2e": {"value": pairs_s, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------- B200 arm
+RESULT_FIELDS = ("status", "count", "metrics", "F", "pack_off", "query_idx", "train_idx", "sq_dist",
+                 "inlier_mask", "sym_err", "pts1", "pts2")
+
+
+def pair_digests(res):
+    """One digest per pair over everything the path outputs for it (status, count, F, metrics, lists)."""
+    out = []
+    for p in range(len(res.status)):
+        sl = res.pair_slice(p)
+        h = hashlib.sha256()
+        for a in (res.status[p:p + 1], res.count[p:p + 1], res.F[p], res.metrics[p:p + 1], res.query_idx[sl],
+                  res.train_idx[sl], res.sq_dist[sl], res.inlier_mask[sl], res.sym_err[sl], res.pts1[sl],
+                  res.pts2[sl]):
+            h.update(np.ascontiguousarray(a).tobytes())
+        out.append(h.hexdigest()[:16])
+    return out
+
+
+def parity_sample(eng, L, host_desc, host_kps, off, pairs, n_check=8, seed=11):
+    """Untimed: `n_check` random pairs of the timed set against the oracle -- cv2's own kNN + ratio loop
+    on the same arrays (lists identical), the reference's verification arithmetic on the GPU's F (masks
+    identical, quality decision equal)."""
+    from oracle import fundamental as ofm
+    from oracle import knn as oknn
+    pick = np.sort(np.random.default_rng(seed).permutation(len(pairs))[:n_check])
+    res = eng.match_pairs(pairs[pick], only_ok=False)
+    knn_ok = ver_ok = True
+    n_ver = 0
+    for p, (i, j) in enumerate(pairs[pick]):
+        a, b = slice(off[i], off[i + 1]), slice(off[j], off[j + 1])
+        q, t, d = oknn.match_features_cv2(host_desc[a], host_desc[b], RATIO)
+        sl = res.pair_slice(p)
+        knn_ok &= bool(np.array_equal(res.query_idx[sl], q) and np.array_equal(res.train_idx[sl], t)
+                       and np.array_equal(res.distance(p), d))
+        knn_ok &= bool(np.array_equal(res.pts1[sl], host_kps[a][q]) and np.array_equal(res.pts2[sl], host_kps[b][t]))
+        if res.status[p] in (L.PAIR_OK, L.PAIR_QUALITY_FAIL):
+            v = ofm.geometric_verification(res.pts1[sl], res.pts2[sl], res.F[p])
+            ver_ok &= bool(np.array_equal(v["inlier_mask"], res.inlier_mask[sl]))
+            ver_ok &= bool(ofm.verify_match_quality(v) == (res.status[p] == L.PAIR_OK))
+            n_ver += 1
+    return {"pairs": int(len(pick)), "knn_ratio_lists_identical_to_cv2": knn_ok,
+            "verification_pairs": n_ver, "verification_identical_given_F": ver_ok,
+            "oracle": "oracle.knn.match_features_cv2 + oracle.fundamental.geometric_verification"}
 
 
 def run_b200(args):
@@ -219,17 +272,50 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    wl = workload(world)
+    def sum_over_ranks(*xs):
+        if world == 1:
+            return [int(x) for x in xs]
+        t = torch.tensor(list(xs), dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        return [int(v) for v in t.tolist()]
+
+    gen_threads = max(2, (os.cpu_count() or 2) // max(world, 1))
+
+    def host_block(wl, pin=True):
+        """This rank's image block, generated on the host: (desc, kps, counts)."""
+        n = wl["n_images"]
+        b0, b1 = D.image_blocks(n, world)[rank]
+        sc = synth.make_scene(n, wl["n_desc"], synth.BASE_SEED + wl["seed_off"], tie_frac=TIE_FRAC)
+        imgs = synth.make_images(sc, range(b0, b1), threads=gen_threads)
+        cnt = np.array([len(d) for d, _ in imgs], np.int64)
+        tot = int(cnt.sum())
+        hd = torch.empty((tot, 128), dtype=torch.uint8, pin_memory=pin)
+        hk = torch.empty((tot, 2), dtype=torch.float32, pin_memory=pin)
+        o = np.concatenate([[0], np.cumsum(cnt)])
+        for i, (d, k) in enumerate(imgs):
+            hd.numpy()[o[i]:o[i + 1]] = d
+            hk.numpy()[o[i]:o[i + 1]] = k
+        return hd, hk, cnt
+
+    def replicate(hd, hk, cnt):
+        d = hd.to(dev, non_blocking=True)
+        k = hk.to(dev, non_blocking=True)
+        if world > 1:
+            return D.replicate_images(d, k, cnt)            # NCCL all-gather over NVLink
+        o = np.zeros(len(cnt) + 1, np.int64)
+        o[1:] = np.cumsum(cnt)
+        return d, k, o
+
+    wl = workload(args.workload)
     n = wl["n_images"]
-    seed = synth.BASE_SEED + (1 if n == 36 else 2)
-    s = synth.make_image_set(n, N_DESC, seed=seed, device=dev, tie_frac=0.01)   # synthetic, untimed
-    off = s.offsets.numpy()
+    h_desc, h_kps, my_counts = host_block(wl)                 # synthetic inputs, untimed
+    desc, kps, off = replicate(h_desc, h_kps, my_counts)
     counts = np.diff(off)
     pairs = all_pairs(n)
     lo, hi = D.partition_pairs(pairs, counts, world)[rank]
     my_pairs = pairs[lo:hi]
     eng = PairEngine(local_rank, mutual=bool(args.mutual))
-    eng.set_images(s.desc, s.kps, off)
+    eng.set_images(desc, kps, off)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)               # > 126 MB L2
 
     # ---------------------------------------------------------- device-resident steps
@@ -246,103 +332,200 @@ def run_b200(args):
             chunks = eng.match_device(my_pairs)
             e1.record()
         barrier()
-    launches = eng.ctx.launches - launches0
-    ms_total = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in ev))
-    ms_step = ms_total / args.steps
-    n_ok = sum(int((c["status"] == L.PAIR_OK).sum().item()) for c in chunks)
-    if world > 1:
-        t_ok = torch.tensor([n_ok], dtype=torch.int64, device=dev)
-        dist.all_reduce(t_ok)
-        n_ok = int(t_ok.item())
-    pairs_s = len(pairs) / (ms_step * 1e-3)
-    cmp_s = float((counts[pairs[:, 0]].astype(np.float64) * counts[pairs[:, 1]]).sum()) / (ms_step * 1e-3)
+        launches = eng.ctx.launches - launches0
+        ms_total = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in ev))
+        ms_step = ms_total / args.steps
+        n_ok = sum(int((c["status"] == L.PAIR_OK).sum().item()) for c in chunks)
+        n_matches = sum(int(c["count"].sum().item()) for c in chunks)
+        hyp_pts = 0.0
+        for c in chunks:
+            m = L.metrics_to_numpy(c["metrics"])
+            hyp_pts += float((m["ransac_iters"].astype(np.float64) * m["total_matches"]).sum())
+        n_ok, n_matches = sum_over_ranks(n_ok, n_matches)
+        del chunks
+        pairs_s = len(pairs) / (ms_step * 1e-3)
+        total_cmp = float((counts[pairs[:, 0]].astype(np.float64) * counts[pairs[:, 1]]).sum())
+        cmp_s = total_cmp / (ms_step * 1e-3)
 
-    # ---------------------------------------------------------- dominant kernel alone (roofline)
-    clk_rows_step = list(clk.rows)
-    first = next(iter(eng._chunks(my_pairs)))
-    kp = my_pairs[first[0]:first[1]]
-    ro = eng.ctx.query_rows(kp)
-    kbuf = eng._buf("knn", (int(ro[-1]), 4), torch.int32)
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local_rank) as clk_k:
+        # ------------------------------------------------------ per-stage split of one step (untimed pass)
+        st_local = eng.stage_times(my_pairs)
+        stages = {k: round(max_over_ranks(v), 4) for k, v in sorted(st_local.items())}
+
+        # ------------------------------------------------------ dominant kernel alone (roofline)
+        first = next(iter(eng._chunks(my_pairs)))
+        kp = my_pairs[first[0]:first[1]]
+        ro = eng.ctx.query_rows(kp)
+        kbuf = eng._buf("knn", (int(ro[-1]), 4), torch.int32)
+        k_steps = max(3, min(args.steps, 10))
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k_steps)]
         for e0, e1 in kev:
             flush.zero_()
             e0.record()
             eng.ctx.knn2(kp, ro, kbuf)
             e1.record()
         torch.cuda.synchronize()
-
-        def same_load():
+        k_ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in kev]))
+        k_ops = OPS_PER_CMP * float((counts[kp[:, 0]].astype(np.float64) * counts[kp[:, 1]]).sum())
+        k_tops = k_ops / (k_ms * 1e-3) / 1e12
+        probe_tops, _ = eng.ctx.probe_int8_peak(4096)
+        t_wait = time.perf_counter()
+        while len(clk.rows) < 5 and time.perf_counter() - t_wait < 6.0:   # short runs: let the sampler see the load
             eng.ctx.knn2(kp, ro, kbuf)
             torch.cuda.synchronize()
-        clk_k.rows = clk_rows_step + clk_k.rows    # clocks under load: timed steps + kernel-alone region
-        clk_extended = clk_k.extend_until(5, same_load)
-    clk.rows = clk_k.rows
-    k_ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in kev]))
-    k_ops = OPS_PER_CMP * float((counts[kp[:, 0]].astype(np.float64) * counts[kp[:, 1]]).sum())
-    k_tops = k_ops / (k_ms * 1e-3) / 1e12
-    probe_tops, _ = eng.ctx.probe_int8_peak(4096)
+    clocks = dict(clk.summary(), window="timed steps + stage split + kernel-alone region")
 
     # ---------------------------------------------------------- end to end through the public call
-    blocks = D.image_blocks(n, world)
-    b0, b1 = blocks[rank]
-    h_desc = s.desc[off[b0]:off[b1]].cpu().pin_memory()
-    h_kps = s.kps[off[b0]:off[b1]].cpu().pin_memory()
-    my_counts = counts[b0:b1]
     h2d = h_desc.numel() + h_kps.numel() * 4
 
-    def e2e_step():
-        d = h_desc.to(dev, non_blocking=True)
-        k = h_kps.to(dev, non_blocking=True)
-        if world > 1:
-            d, k, o = D.replicate_images(d, k, my_counts)      # NCCL all-gather over NVLink
-        else:
-            o = off
+    def upload():
+        d, k, o = replicate(h_desc, h_kps, my_counts)
         eng.set_images(d, k, o)
-        if world == 1:
-            res = eng.match_pairs(my_pairs)                    # host-side results (D2H inside)
-            return sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
-                                                        "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1",
-                                                        "pts2"))
-        # N > 1, as ImageMatcher's rank path: every rank brings the match lists of ITS pairs to its own
-        # host memory (it writes those files); only the per-pair status / metrics rows meet on rank 0
-        res = eng.match_pairs(my_pairs)
-        nbytes = sum(getattr(res, f).nbytes for f in ("status", "count", "metrics", "F", "pack_off", "query_idx",
-                                                      "train_idx", "sq_dist", "inlier_mask", "sym_err", "pts1", "pts2"))
-        rows = torch.from_numpy(np.ascontiguousarray(res.metrics).view(np.uint8).reshape(len(my_pairs), -1)).to(dev)
-        D.gather_to_root(rows)
-        D.gather_to_root(torch.from_numpy(np.ascontiguousarray(res.status)).to(dev))
+        return d, k
+
+    def res_bytes(res):
+        return sum(getattr(res, f).nbytes for f in RESULT_FIELDS)
+
+    def e2e_rank_path():
+        """ImageMatcher's path: every rank fetches the match lists of ITS pairs to its own pinned host
+        memory (it writes those files); only the per-pair rows meet on rank 0."""
+        upload()
+        res = eng.match_pairs(my_pairs)                        # host-side results (D2H inside)
+        if world > 1:
+            rows = np.concatenate([np.ascontiguousarray(res.metrics).view(np.uint8).reshape(len(my_pairs), -1),
+                                   np.ascontiguousarray(res.status).view(np.uint8).reshape(len(my_pairs), -1)], 1)
+            D.gather_to_root(torch.from_numpy(rows).to(dev))
+        return res_bytes(res)
+
+    def e2e_root_gather():
+        """The north-star wording: match lists of every rank gathered on rank 0 over NCCL (one grouped
+        send/recv sized from an all-gathered count vector), rank 0 alone copies them to the host."""
+        upload()
+        local = eng.match_pairs_device(my_pairs)
+        got = D.gather_batch_results(local)
+        nbytes = 0
+        if got is not None:
+            flat = {k: v for k, v in got.items() if k != "dense"}
+            flat.update(got["dense"])
+            host = eng._to_host(flat)
+            nbytes = sum(a.nbytes for a in host.values())
         return nbytes
 
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    d2h = 0
-    for _ in range(args.steps):
-        d2h = e2e_step()
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0) / args.steps
-    if world > 1:                                              # bytes of all ranks
-        t_b = torch.tensor([d2h, h2d], dtype=torch.int64, device=dev)
-        dist.all_reduce(t_b)
-        d2h, h2d = int(t_b[0].item()), int(t_b[1].item())
+    def time_e2e(fn):
+        fn()
+        barrier()
+        t0 = time.perf_counter()
+        nb = 0
+        for _ in range(args.steps):
+            nb = fn()
+        barrier()
+        return max_over_ranks(time.perf_counter() - t0) / args.steps, nb
+
+    e2e_s, d2h = time_e2e(e2e_rank_path)
+    d2h, h2d_all = sum_over_ranks(d2h, h2d)
     e2e_pairs_s = len(pairs) / e2e_s
+    e2e_variants = {"per_rank_fetch_rows_to_rank0": e2e_pairs_s}
+    if world > 1:
+        root_s, root_bytes = time_e2e(e2e_root_gather)
+        e2e_variants["match_lists_gathered_on_rank0"] = len(pairs) / root_s
+        e2e_variants["rank0_gather_d2h_bytes_per_step"] = sum_over_ranks(root_bytes)[0]
+
+    # ---------------------------------------------------------- parity of the timed set (untimed)
+    desc, kps = upload()
+    parity = None
+    if not args.no_parity:
+        if rank == 0:
+            hd_all = desc.cpu().numpy() if world > 1 else h_desc.numpy()
+            hk_all = kps.cpu().numpy() if world > 1 else h_kps.numpy()
+            parity = parity_sample(eng, L, hd_all, hk_all, off, my_pairs, n_check=args.parity_pairs)
+        if world > 1:
+            # rank independence: every rank digests the first pairs of its range; rank 0 recomputes them
+            ns = min(24, len(my_pairs))
+            mine = pair_digests(eng.match_pairs(my_pairs[:ns], only_ok=False))
+            parts = D.all_gather_objects((lo, ns, mine))
+            if rank == 0:
+                same, total = 0, 0
+                for (plo, pn, dig) in parts[1:]:
+                    again = pair_digests(eng.match_pairs(pairs[plo:plo + pn], only_ok=False))
+                    same += sum(a == b for a, b in zip(again, dig))
+                    total += pn
+                parity["ranks_vs_rank0_recompute"] = {
+                    "pairs": total, "identical": same,
+                    "what": "sha256 over status, count, F, metrics and all match arrays, per pair"}
+            barrier()
+
+    # ---------------------------------------------------------- the configurations the target names
+    target = {}
+    tkeys = []
+    if args.target_config == "auto":
+        tkeys = ["1000x8k"] + (["500x32k"] if world >= 8 else [])
+    elif args.target_config not in ("none", ""):
+        tkeys = args.target_config.split(",")
+    for tk in tkeys:
+        twl = workload(tk)
+        del desc, kps
+        eng.set_images(torch.zeros((0, 128), dtype=torch.uint8, device=dev),
+                       torch.zeros((0, 2), dtype=torch.float32, device=dev), np.zeros(1, np.int64))
+        torch.cuda.empty_cache()
+        thd, thk, tcnt = host_block(twl, pin=False)
+        desc, kps, toff = replicate(thd, thk, tcnt)
+        del thd, thk
+        tcounts = np.diff(toff)
+        tpairs = all_pairs(twl["n_images"])
+        tlo, thi = D.partition_pairs(tpairs, tcounts, world)[rank]
+        eng.set_images(desc, kps, toff)
+        mine = tpairs[tlo:thi]
+        eng.match_device(mine[:max(1, len(mine) // 50)])       # warm-up on 2 % of the pairs
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush.zero_()
+        e0.record()
+        tch = eng.match_device(mine)
+        e1.record()
+        barrier()
+        t_ms = max_over_ranks(e0.elapsed_time(e1))
+        t_ok = sum_over_ranks(sum(int((c["status"] == L.PAIR_OK).sum().item()) for c in tch))[0]
+        del tch
+        st = eng.stage_times(mine[:max(1, len(mine) // 8)])
+        ops = OPS_PER_CMP * float((tcounts[tpairs[:, 0]].astype(np.float64) * tcounts[tpairs[:, 1]]).sum())
+        knn_frac = max_over_ranks(st["knn"] / max(st["total"], 1e-9))
+        whole = ops / (t_ms * 1e-3) / 1e12
+        target[tk] = {
+            "config": config_of(twl, args.mutual), "steps": 1, "warmup": "2 % of the pairs",
+            "ms_per_step": t_ms, "pairs_per_sec": twl["pairs"] / (t_ms * 1e-3),
+            "whole_step_int8_tops": whole,
+            "whole_step_frac_of_nominal_int8": whole / (NOMINAL_INT8_TOPS * world),
+            "knn_share_of_step": round(knn_frac, 4),
+            "knn_kernel_int8_tops_per_gpu": whole / world / max(knn_frac, 1e-9),
+            "pairs_passing_verification": t_ok,
+        }
 
     # ---------------------------------------------------------- CPU baseline (rank 0, N = 1)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        nd = 6
-        done, secs, cores = cpu_reference_sample(s.desc[:off[nd]].cpu().numpy(), s.kps[:off[nd]].cpu().numpy(), off,
-                                                 all_pairs(nd), budget_s=20.0, max_pairs=15)
-        cpu = {"value": done / secs, "unit": "pairs/s", "cores": cores, "kind": "port",
-               "sample": f"{done} pairs of the workload (first {nd} images, 8192x8192 descriptors each) through the "
-                         "reference's OpenCV calls restated in oracle/pipeline.py (BFMatcher.knnMatch k=2 + ratio loop + "
-                         "findFundamentalMat FM_RANSAC + geometric_verification)"}
+        import cv2
+        cores = os.cpu_count() or 1
+        cv2.setNumThreads(cores)
+        samp = sample_pairs(wl, 64)
+        hd, hk = h_desc.numpy(), h_kps.numpy()
+        o0 = np.concatenate([[0], np.cumsum(my_counts)])
+        images = {int(i): (hd[o0[i]:o0[i + 1]], hk[o0[i]:o0[i + 1]]) for i in set(samp.ravel().tolist())}
+        cpu_pairs(images, samp[:2])                            # warm-up
+        secs = cpu_pairs(images, samp, mutual=bool(args.mutual))
+        cpu = {"value": len(samp) / secs, "unit": "pairs/s", "cores": min(cores, cv2.getNumThreads()), "kind": "port",
+               "sample": f"{len(samp)} pairs drawn with a fixed seed from the workload's {wl['pairs']} pairs (the arrays "
+                         "the B200 arm matched) through the reference's OpenCV calls restated in oracle/pipeline.py "
+                         "(BFMatcher.knnMatch k=2 + ratio loop + findFundamentalMat FM_RANSAC + "
+                         f"geometric_verification), {secs:.1f} s"}
 
     if rank == 0:
         peaks = {}
         try:
             peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        int8_peak = None
+        try:
+            int8_peak = json.loads((ROOT / "profiles" / "int8_peak.json").read_text())
         except Exception:
             pass
         traffic = None
@@ -352,28 +535,44 @@ def run_b200(args):
                 traffic = json.loads(tp.read_text()).get("dram_bytes_per_launch")
             except Exception:
                 traffic = None
+        peak = float(int8_peak["int8_tops_measured"]) if int8_peak else NOMINAL_INT8_TOPS
+        whole_tops = cmp_s * OPS_PER_CMP / 1e12
+        ransac_ms = st_local.get("ransac", 0.0)
         line = {
             "metric": "image_pairs_per_sec", "value": pairs_s, "unit": "pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": wl["name"], "mutual_nn": bool(args.mutual), "ratio": 0.75,
-                       "pairs": int(len(pairs)), "pairs_passing_verification": n_ok,
-                       "parallelism": f"pair-partition x{world}", "l2": "flushed between steps (256 MiB write)",
-                       "note": "N=1 runs BASELINE configs[1] (36x8k); N>1 runs configs[2] (200x8k) split over the ranks"},
-            "comparisons_per_sec": cmp_s, "int8_tops": cmp_s * OPS_PER_CMP / 1e12,
-            "roofline": {"bound": "tensor", "achieved": k_tops, "peak": NOMINAL_INT8_TOPS, "unit": "TOP/s",
-                         "frac": k_tops / NOMINAL_INT8_TOPS, "traffic": traffic,
-                         "kernel": "knn2_wide_kernel (TMA + tcgen05 kind::i8 128x256x32, fused top-2 epilogue) + its fix-up pass",
-                         "kernel_ms": k_ms,
-                         "peak_source": "nominal dense int8 (MEASURED_PEAKS.json has no int8 entry); "
-                                        f"MMA-only tcgen05 probe measured live: {probe_tops:.0f} TOP/s; "
-                                        f"MEASURED bf16 {peaks.get('bf16_tflops')} TFLOP/s, HBM {peaks.get('hbm_gbs')} GB/s",
+            "config": config_of(wl, args.mutual),
+            "run": {"pairs_passing_verification": n_ok, "matches_after_ratio": n_matches,
+                    "parallelism": f"pair list cut into {world} contiguous ranges of equal n_i*n_j",
+                    "l2": "flushed between steps (256 MiB write)",
+                    "ransac_hypotheses_x_points_per_sec_rank0": hyp_pts / (ransac_ms * 1e-3) if ransac_ms > 0 else None},
+            "comparisons_per_sec": cmp_s, "int8_tops": whole_tops,
+            "whole_step_frac_of_nominal_int8": whole_tops / (NOMINAL_INT8_TOPS * world),
+            "stages_ms": stages,
+            "roofline": {"bound": "tensor", "achieved": k_tops, "peak": peak, "unit": "TOP/s",
+                         "frac": k_tops / peak, "frac_of_nominal_4500": k_tops / NOMINAL_INT8_TOPS,
+                         "traffic": traffic,
+                         "kernel": "knn2_wide_kernel (TMA + tcgen05 kind::i8 128x256x32, two accumulators in TMEM, "
+                                   "norm-fold K step, fused top-2 epilogue) + its fix-up pass",
+                         "kernel_ms": k_ms, "kernel_pairs": int(len(kp)),
+                         "algorithmic_ops_per_launch": k_ops,
+                         "peak_source": ("measured: MMA-only tcgen05 kind::i8 loop on every SM, profiles/int8_peak.json "
+                                         "(MEASURED_PEAKS.json has no int8 entry; nominal dense int8 4500)"
+                                         if int8_peak else "nominal dense int8 (no measured int8 peak on file)") +
+                                        f"; same probe live in this run: {probe_tops:.0f} TOP/s; MEASURED bf16 "
+                                        f"{peaks.get('bf16_tflops')} TFLOP/s, HBM {peaks.get('hbm_gbs')} GB/s",
                          "probe_tops": probe_tops},
-            "e2e": {"value": e2e_pairs_s, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "e2e": {"value": e2e_pairs_s, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d_all),
+                    "d2h_bytes_per_step": int(d2h)},
+            "e2e_variants": e2e_variants,
             "gpu_launches": int(launches),
-            "clocks": dict(clk.summary(), window="timed steps + kernel-alone region" +
-                           (" + untimed continuation of the same kernel (sampler start-up)" if clk_extended else "")),
+            "clocks": clocks,
         }
+        if parity:
+            line["parity_check"] = parity
+        if target:
+            line["target_config"] = target
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
@@ -384,10 +583,15 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--mutual", type=int, default=0, help="1: add the mutual-NN check (second, reversed kNN pass)")
+    ap.add_argument("--workload", default="200x8k", choices=sorted(WORKLOADS))
+    ap.add_argument("--mutual", type=int, default=0, help="1: add the mutual-NN check")
+    ap.add_argument("--target-config", default="auto",
+                    help="auto (1000x8k; + 500x32k at 8 GPUs), none, or a comma list of workload keys")
+    ap.add_argument("--parity-pairs", type=int, default=8)
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.steps = max(1, args.steps)

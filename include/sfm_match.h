@@ -269,6 +269,19 @@ SFM_API int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_w
  * issue, bit 2 the wide kernel runs without its fix-up pass.  Test switch (results stay exact):
  * bit 3 shrinks the wide kernel's fix-up list to 4 entries, so its overflow scan is exercised. */
 SFM_API int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags);
+/* Profiling build of the TS kNN kernel: enable != 0 makes the following sfm_knn2 calls run the
+ * instrumented variant (clock64 counters around every barrier wait).  h_sum16 (may be NULL) receives
+ * the counters of the last instrumented launch summed over the CTAs (layout: knn_ts.cu); synchronises. */
+SFM_API int sfm_debug_knn_profile(sfm_ctx* ctx, int32_t enable, int64_t* h_sum16, void* stream);
+/* Hand-over latency probe (one CTA): n_mma tcgen05.mma (128 x tile_n x 32, tile_n = 128 or 256) + commit by
+ * one warp, a second warp waits and answers through a plain mbarrier.  h_out4 = mean cycles of: issue,
+ * issue start -> other warp woken, its arrive -> issuer woken, issue start -> issuer itself woken.
+ * trail > 0: that many more MMAs (another accumulator) are issued right after the commit. */
+SFM_API int sfm_debug_handover_probe(sfm_ctx* ctx, int32_t iters, int32_t n_mma, int32_t tile_n, int32_t trail,
+                             int64_t* h_out4, void* stream);
+/* Time stamps of CTA 0's first 4096 accumulator groups in the last instrumented launch:
+ * h_events i64 [5][4096] (kinds: knn_ts.cu).  Synchronises. */
+SFM_API int sfm_debug_knn_profile_events(sfm_ctx* ctx, int64_t* h_events, void* stream);
 /* Reads (synchronising `stream`) whether the registered set exceeded the fold range. */
 SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);
 

@@ -108,10 +108,12 @@ struct sfm_ctx {
     bool have_tmap = false;
     DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
+    DevBuf<long long> d_prof;      // cycle counters of the TS kernel's profiling build (sfm_debug_knn_profile)
+    bool knn_prof = false;
     DevBuf<uint32_t> d_par_bits;   // norm parities of the padded column space, 32 per word (knn_ts.cu)
     DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
-    int knn_auto = 8;            // what mode 0 resolves to: 8 = TS kernel + generic, 5 = wide fold + generic
+    int knn_auto = 5;            // what mode 0 resolves to: 5 = wide fold kernel + generic, 8 = TS kernel + generic
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
@@ -264,6 +266,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_bias.release();
     ctx->d_bias32.release();
     ctx->d_par_bits.release();
+    ctx->d_prof.release();
     ctx->d_fix_list.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
@@ -405,11 +408,16 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
+    if (km >= 8 && ctx->knn_prof) {
+        SFM_CUDA(ctx, ctx->d_prof.reserve(static_cast<size_t>(ctx->num_sms) * 16 + 5 * 4096));
+        SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_prof.p, 0, sizeof(long long) * (ctx->num_sms * 16 + 5 * 4096), st));
+    }
     if (km >= 8)
         r = sfm::launch_knn2_ts(ctx->tmap, ctx->tmap_ax32, ctx->d_desc, ctx->d_bias32.p, ctx->d_work.p, n_work,
                                 ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
                                 km == 10 ? 1 : (km == 11 ? 2 : 0), ctx->knn_mode != 0, ctx->knn_tuning,
-                                ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches);
+                                ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches,
+                                ctx->knn_prof ? ctx->d_prof.p : nullptr);
     else if (km >= 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
@@ -801,7 +809,7 @@ int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
 
 int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags) {
     if (!ctx) return 1;
-    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 15u;
+    ctx->knn_tuning.probe_flags = static_cast<uint32_t>(flags) & 0x7FFu;
     return 0;
 }
 
@@ -810,6 +818,51 @@ int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_wait_ns) 
     if (wait_ns < 0 || epi_wait_ns < 0) return ctx->fail("wait hints must be >= 0");
     ctx->knn_tuning.wait_ns = static_cast<uint32_t>(wait_ns);
     ctx->knn_tuning.epi_wait_ns = static_cast<uint32_t>(epi_wait_ns);
+    return 0;
+}
+
+int sfm_debug_handover_probe(sfm_ctx* ctx, int32_t iters, int32_t n_mma, int32_t tile_n, int32_t trail, int64_t* h_out4,
+                             void* stream) {
+    if (!ctx || !h_out4) return 1;
+    if (iters < 1 || n_mma < 0 || n_mma > 64 || trail < 0 || trail > 64 || (tile_n != 128 && tile_n != 256))
+        return ctx->fail("bad probe arguments");
+    if (trail > 0 && tile_n != 128) return ctx->fail("trailing MMAs need tile_n = 128 (they use columns 128..255)");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, ctx->d_meta.reserve(8));
+    int r = sfm::launch_handover_probe(iters, n_mma, tile_n, trail, reinterpret_cast<long long*>(ctx->d_meta.p), st, &ctx->launches);
+    if (r) return ctx->fail("probe launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_out4, ctx->d_meta.p, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA(ctx, cudaStreamSynchronize(st));
+    return 0;
+}
+
+int sfm_debug_knn_profile_events(sfm_ctx* ctx, int64_t* h_events, void* stream) {
+    if (!ctx || !h_events) return 1;
+    if (!ctx->d_prof.p) return ctx->fail("no profile recorded");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_events, ctx->d_prof.p + static_cast<size_t>(ctx->num_sms) * 16,
+                                  sizeof(long long) * 5 * 4096, cudaMemcpyDeviceToHost,
+                                  static_cast<cudaStream_t>(stream)));
+    SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int sfm_debug_knn_profile(sfm_ctx* ctx, int32_t enable, int64_t* h_sum16, void* stream) {
+    if (!ctx) return 1;
+    if (h_sum16) {
+        for (int i = 0; i < 16; ++i) h_sum16[i] = 0;
+        if (ctx->d_prof.p) {
+            SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+            std::vector<long long> h(static_cast<size_t>(ctx->num_sms) * 16);
+            SFM_CUDA(ctx, cudaMemcpyAsync(h.data(), ctx->d_prof.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost,
+                                          static_cast<cudaStream_t>(stream)));
+            SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+            for (int b = 0; b < ctx->num_sms; ++b)
+                for (int i = 0; i < 16; ++i) h_sum16[i] += h[static_cast<size_t>(b) * 16 + i];
+        }
+    }
+    ctx->knn_prof = enable != 0;
     return 0;
 }
 

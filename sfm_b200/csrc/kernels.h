@@ -71,7 +71,8 @@ int launch_knn2_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uin
                    const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
                    const uint32_t* d_par_bits, int32_t* d_flags, int variant, int force, const struct KnnTuning& tn,
                    int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st,
-                   int64_t* launches);
+                   int64_t* launches, long long* d_prof = nullptr);
+int launch_handover_probe(int iters, int n_mma, int tile_n, int trail, long long* d_out, cudaStream_t st, int64_t* launches);
 int launch_ts_rate_probe(int groups, int tile_n, int ts, int commit, int num_sms, cudaStream_t st,
                          int64_t* launches);
 

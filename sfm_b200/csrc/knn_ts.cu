@@ -252,6 +252,7 @@ struct Trk {
 struct KeyFmt {
     uint32_t sh, mul, ubits;   // key = (m >> sh) * mul + (uidrev << 1) + slot, mul = 2^(ubits+1)
     int n_units;               // units per thread over the whole work item (2 per train tile)
+    bool no_park;              // timing probe: skip the parking stores (results become meaningless)
 };
 
 struct Top2K {
@@ -274,14 +275,14 @@ __device__ __forceinline__ void top2k_insert_ordered(Top2K& s, int key, int col)
     }
 }
 
-// Maximum of 16 folded accumulators (in place; MASKED: columns >= t_cnt count as 0).
-template <bool MASKED>
-__device__ __forceinline__ int chunk_max(uint32_t (&acc)[16], int col0, int t_cnt) {
+// Maximum of the 16 folded accumulators acc[OFF..OFF+16) (in place; MASKED: columns >= t_cnt count as 0).
+template <bool MASKED, int OFF>
+__device__ __forceinline__ int chunk_max(uint32_t (&acc)[64], int col0, int t_cnt) {
     int v[16];
 #pragma unroll
     for (int e = 0; e < 16; ++e) {
-        if (MASKED) acc[e] = (col0 + e < t_cnt) ? acc[e] : 0u;
-        v[e] = static_cast<int>(acc[e]);
+        if (MASKED) acc[OFF + e] = (col0 + OFF + e < t_cnt) ? acc[OFF + e] : 0u;
+        v[e] = static_cast<int>(acc[OFF + e]);
     }
     const int a0 = __vimax3_s32(v[0], v[1], v[2]), a1 = __vimax3_s32(v[3], v[4], v[5]);
     const int a2 = __vimax3_s32(v[6], v[7], v[8]), a3 = __vimax3_s32(v[9], v[10], v[11]);
@@ -289,21 +290,19 @@ __device__ __forceinline__ int chunk_max(uint32_t (&acc)[16], int col0, int t_cn
     return max(__vimax3_s32(a0, a1, a2), __vimax3_s32(a3, a4, v[15]));
 }
 
-// One 32-column unit: lo / hi are its two 16-column chunks, m their maximum, ulow = uidrev << 1.
-template <bool SH0>
-__device__ __forceinline__ void unit_update(Trk& s, const uint32_t (&lo)[16], const uint32_t (&hi)[16], int m,
-                                            uint32_t slots, const KeyFmt& kf, uint32_t ulow) {
+// One 32-column unit acc[OFF..OFF+32): m its maximum, ulow = uidrev << 1.
+template <bool SH0, int OFF>
+__device__ __forceinline__ void unit_update(Trk& s, const uint32_t (&acc)[64], int m, uint32_t slots,
+                                            const KeyFmt& kf, uint32_t ulow) {
     const uint32_t sb = s.k2 & 1u;
     const uint32_t low = sb | ulow;
     const uint32_t key = SH0 ? static_cast<uint32_t>(m) * 512u + low
                              : (static_cast<uint32_t>(m) >> kf.sh) * kf.mul + low;
-    if (key > s.k2) {
+    if (key > s.k2 && !kf.no_park) {
         const uint32_t dst = slots + sb * kSlotStride;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) sts128(dst + g * kSlotRow, lo[4 * g], lo[4 * g + 1], lo[4 * g + 2], lo[4 * g + 3]);
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-            sts128(dst + (4 + g) * kSlotRow, hi[4 * g], hi[4 * g + 1], hi[4 * g + 2], hi[4 * g + 3]);
+        for (int g = 0; g < 8; ++g)
+            sts128(dst + g * kSlotRow, acc[OFF + 4 * g], acc[OFF + 4 * g + 1], acc[OFF + 4 * g + 2], acc[OFF + 4 * g + 3]);
     }
     const uint32_t t1 = min(s.k1, key);
     s.k1 = max(s.k1, key);
@@ -444,51 +443,68 @@ __device__ __forceinline__ void load_a_half(uint32_t (&a)[16], const uint8_t* __
     }
 }
 
-// One accumulator group of this thread: 64 columns as four 16-column TMEM loads (one in flight while
-// the previous chunk is reduced), two 32-column units.  The stage is handed back to the MMA warp as
-// soon as the last load has landed.
+// One accumulator group of this thread: its 64 columns come out of TMEM in ONE load and the stage goes
+// back to the MMA warp as soon as they have landed -- the MMA -> epilogue -> MMA chain of a stage then
+// holds one TMEM round trip instead of the whole reduction (measured: the stage was held 560 cycles with
+// four 16-column loads interleaved with the work, and the hand-over round trip itself is ~800).  The two
+// 32-column units are reduced from registers afterwards, overlapping the next groups' MMAs.
 template <bool MASKED, bool SH0, int MODE>
 __device__ __forceinline__ void process_group(Trk& sk, uint32_t taddr, int t, int t_cnt, int colbase, uint32_t my_slots,
-                                              const KeyFmt& kf, uint64_t* empty, int lane) {
-    uint32_t b0[16], b1[16], b2[16];
+                                              const KeyFmt& kf, uint64_t* empty, int lane, long long* ev3 = nullptr,
+                                              long long ev_base = 0) {
+    uint32_t b[64];
     const uint32_t ut = static_cast<uint32_t>(kf.n_units - 1 - t * kUnitsPerTile) << 1;
     const int col0 = t * NT + colbase;
-    tmem_ld_32x16(taddr, b0);
-    tmem_ld_wait();
-    tmem_ld_32x16(taddr + 16, b1);
-    int ma = chunk_max<MASKED>(b0, col0, t_cnt);
-    tmem_ld_wait();
-    tmem_ld_32x16(taddr + 32, b2);
-    int mb = chunk_max<MASKED>(b1, col0 + 16, t_cnt);
-    if (MODE == 1) {
-        sk.k1 = max(sk.k1, static_cast<uint32_t>(max(ma, mb)));
-    } else if (!MASKED || col0 < t_cnt) {
-        unit_update<SH0>(sk, b0, b1, max(ma, mb), my_slots, kf, ut);
-    }
-    tmem_ld_wait();
-    tmem_ld_32x16(taddr + 48, b0);
-    ma = chunk_max<MASKED>(b2, col0 + 32, t_cnt);
+    tmem_ld_32x64(taddr, b);
     tmem_ld_wait();
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(empty);
-    mb = chunk_max<MASKED>(b0, col0 + 48, t_cnt);
-    if (MODE == 1) {
-        sk.k1 = max(sk.k1, static_cast<uint32_t>(max(ma, mb)));
-    } else if (!MASKED || col0 + kUnit < t_cnt) {
-        unit_update<SH0>(sk, b2, b0, max(ma, mb), my_slots, kf, ut ^ 2u);
+    if (ev3 && lane == 0) *ev3 = clock64() - ev_base;
+    {
+        const int ma = chunk_max<MASKED, 0>(b, col0, t_cnt), mb = chunk_max<MASKED, 16>(b, col0, t_cnt);
+        if (MODE == 1) {
+            sk.k1 = max(sk.k1, static_cast<uint32_t>(max(ma, mb)));
+        } else if (!MASKED || col0 < t_cnt) {
+            unit_update<SH0, 0>(sk, b, max(ma, mb), my_slots, kf, ut);
+        }
+    }
+    {
+        const int ma = chunk_max<MASKED, 32>(b, col0, t_cnt), mb = chunk_max<MASKED, 48>(b, col0, t_cnt);
+        if (MODE == 1) {
+            sk.k1 = max(sk.k1, static_cast<uint32_t>(max(ma, mb)));
+        } else if (!MASKED || col0 + kUnit < t_cnt) {
+            unit_update<SH0, 32>(sk, b, max(ma, mb), my_slots, kf, ut ^ 2u);
+        }
     }
 }
 
+// Cycle counters of the profiling build (PROF): per CTA, 16 words.
+//  [0] MMA warp: total loop cycles   [1] waiting b_full   [2] waiting t_empty   [3] waiting a_full
+//  [4] producer: waiting b_empty     [5] groups issued
+//  [8] epilogue warp 0: total        [9] waiting t_full   [10] in process_group [11] end of work item (resolve..write)
+//  [12] epilogue warp 0: A refill (st + wait + arrive)
+// plus, for CTA 0, time stamps (cycles since the CTA's start) of the first kProfEvents groups after the
+// counters: [k][g], k = 0 MMA warp passed t_empty, 1 commit issued, 2 epilogue (quadrant 0, lower half of
+// the group's block) passed t_full, 3 it handed the stage back, 4 it finished the group.
+constexpr int kProfEvents = 4096;
+#define SFM_PROF_EV(kind, g) do { if (PROF && blockIdx.x == 0 && lane == 0 && (g) < kProfEvents) \
+    prof_out[gridDim.x * 16 + (kind) * kProfEvents + (g)] = clock64() - prof_base; } while (0)
+#define SFM_PROF_T0() long long prof_t0 = PROF ? clock64() : 0
+#define SFM_PROF_ADD(slot) do { if (PROF) { const long long t1__ = clock64(); prof[slot] += t1__ - prof_t0; prof_t0 = t1__; } } while (0)
+
 // MODE 0: the kNN.  1: max tree only, 2: no epilogue (timing probes; output is not a kNN).
-template <int MODE>
+template <int MODE, bool PROF>
 __global__ void __launch_bounds__(kThreads, 1)
 knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
                const uint8_t* __restrict__ desc, const uint8_t* __restrict__ bias32,
                const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms,
                const int32_t* __restrict__ norms_pad, const uint32_t* __restrict__ par_bits,
-               int32_t* __restrict__ flags, int force, uint32_t probe_flags, int2* __restrict__ fix_list,
-               int fix_cap, int4* __restrict__ out) {
+               int32_t* __restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns, uint32_t epi_wait_ns,
+               int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out, long long* __restrict__ prof_out) {
+    long long prof[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) prof[i] = 0;
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     // flags[0] != 0: some row's norm is beyond the fold range -> the generic kernel runs instead
@@ -522,15 +538,20 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *sm.tmem_slot, 0);
+    const long long prof_base = PROF ? clock64() : 0;
+    // probe bits 8..10: use only this many stages of the train-tile ring (0 = all; a latency probe)
+    const int b_depth = ((probe_flags >> 8) & 7u) ? min(static_cast<int>((probe_flags >> 8) & 7u), kBStages) : kBStages;
 
     if (warp == kProducerWarp) {
-        Pipe bp(kBStages);
+        Pipe bp(b_depth);
         for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
             const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
             const int t_row = w0.z, t_cnt = w0.w;
             const int n_tiles = (t_cnt + NT - 1) / NT;
             for (int t = 0; t < n_tiles; ++t) {
-                mbar_wait(&sm.b_empty[bp.stage], bp.phase ^ 1);
+                SFM_PROF_T0();
+                mbar_wait_suspend(&sm.b_empty[bp.stage], bp.phase ^ 1, wait_ns);
+                SFM_PROF_ADD(4);
                 if (elect_one()) {
                     uint8_t* dst = sm.b + size_t(bp.stage) * kStageBytes;
                     // rows beyond the train image are masked in the epilogue; beyond the array TMA fills zeros
@@ -543,22 +564,30 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                 bp.advance();
             }
         }
+        if (PROF && lane == 0) prof_out[blockIdx.x * 16 + 4] = prof[4];
     } else if (warp == kMmaWarp) {
-        Pipe bp(kBStages);
+        Pipe bp(b_depth);
         uint32_t s = 0, sph = 0;
         int item = 0;
+        const long long prof_begin = PROF ? clock64() : 0;
         for (long long w = blockIdx.x; w < n_work; w += gridDim.x, ++item) {
             const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
             const int n_tiles = (w0.w + NT - 1) / NT;
             for (int t = 0; t < n_tiles; ++t) {
+                SFM_PROF_T0();
                 mbar_wait(&sm.b_full[bp.stage], bp.phase);
+                SFM_PROF_ADD(1);
                 const uint32_t bsm = smem_u32(sm.b + size_t(bp.stage) * kStageBytes);
                 const uint64_t bdesc0 = make_kmajor_sw128_desc(bsm);
                 const uint64_t xdesc = make_kmajor_sw32_desc_ts(bsm + kBTileBytes);
 #pragma unroll
                 for (int a = 0; a < 2; ++a) {
+                    if (PROF) prof_t0 = clock64();
                     if (t == 0) mbar_wait(&sm.a_full[a], item & 1);   // this block's query rows are in TMEM
+                    SFM_PROF_ADD(3);
                     mbar_wait(&sm.t_empty[s], sph ^ 1);
+                    SFM_PROF_ADD(2);
+                    SFM_PROF_EV(0, static_cast<int>(prof[5]));
                     tc_fence_after();
                     const uint32_t d = tmem_base + s * NT;
                     const uint32_t ta = tmem_base + kAColBase + 32 * a;
@@ -573,6 +602,13 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                         if (a == 1) mma_commit(&sm.b_empty[bp.stage]);
                     }
                     __syncwarp();
+                    SFM_PROF_EV(1, static_cast<int>(prof[5]));
+                    if (PROF) prof[5] += 1;
+                    if (PROF && (probe_flags & 16u)) {   // diagnostic: how long until THIS warp sees the group complete
+                        const long long tq = clock64();
+                        mbar_wait(&sm.t_full[s], sph);
+                        prof[6] += clock64() - tq;
+                    }
                     if (++s == kAccStages) {
                         s = 0;
                         sph ^= 1;
@@ -580,6 +616,14 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                 }
                 bp.advance();
             }
+        }
+        if (PROF && lane == 0) {
+            prof_out[blockIdx.x * 16 + 0] = clock64() - prof_begin;
+            prof_out[blockIdx.x * 16 + 1] = prof[1];
+            prof_out[blockIdx.x * 16 + 2] = prof[2];
+            prof_out[blockIdx.x * 16 + 3] = prof[3];
+            prof_out[blockIdx.x * 16 + 5] = prof[5];
+            prof_out[blockIdx.x * 16 + 6] = prof[6];
         }
     } else {
         // ------------------------------------------------ epilogue warps
@@ -611,6 +655,9 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
             if (lane == 0) mbar_arrive(&sm.a_full[blk]);
         }
         int item = 0;
+        const long long prof_begin = PROF ? clock64() : 0;
+        int prof_g = blk;                       // global group index of this block's next group
+        const bool prof_me = PROF && quad == 0 && half == 0;
         for (long long w = blockIdx.x; w < n_work; w += gridDim.x, ++item) {
             const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
             const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
@@ -628,19 +675,23 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                 nq_row = n0.x;
                 nq_cnt = n0.y;
             }
-            const int pre_t = max(n_tiles - 3, 0);      // tile at which the next work item's rows are fetched
+            const int pre_t = n_tiles - 1;              // the next work item's rows are fetched behind the last wait
             KeyFmt kf;
             kf.n_units = n_tiles * kUnitsPerTile;
             kf.ubits = max(32 - __clz(kf.n_units - 1), 8);
             kf.sh = kf.ubits > 8 ? kf.ubits - 8 : 0;   // m < 2^23: (23 - sh) + ubits + 1 <= 32 bits
             kf.mul = 2u << kf.ubits;
+            kf.no_park = (probe_flags & 32u) != 0;
             // units this thread will see: 2 per full tile, fewer in the last, partial one
             const int rem = t_cnt - (n_tiles - 1) * NT - colbase;
             const int n_seen = (n_tiles - 1) * kUnitsPerTile + min(max((rem + kUnit - 1) / kUnit, 0), kUnitsPerTile);
             Trk sk{1, 0, 0, 0};   // empty keys: k1 owns slot 1, k2 slot 0 (the first unit is parked in slot 0)
             for (int t = 0; t < n_tiles; ++t) {
                 if (has_next && t == pre_t) load_a_half(a_next, desc, nq_row, nq_cnt, row, half);
-                mbar_wait(&sm.t_full[s], sph);
+                SFM_PROF_T0();
+                mbar_wait_suspend(&sm.t_full[s], sph, epi_wait_ns);
+                SFM_PROF_ADD(9);
+                if (prof_me) SFM_PROF_EV(2, prof_g);
                 tc_fence_after();
                 if (has_next && t == n_tiles - 1) {
                     // the last group that reads this block's A operand has completed: next rows in
@@ -649,6 +700,7 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sm.a_full[blk]);
+                    SFM_PROF_ADD(12);
                 }
                 uint64_t* empty = &sm.t_empty[s];
                 const uint32_t taddr = lane_base + s * NT + colbase;
@@ -663,14 +715,22 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                     if (lane == 0) mbar_arrive(empty);
                     continue;
                 }
+                long long* ev3 = (prof_me && blockIdx.x == 0 && prof_g < kProfEvents)
+                                     ? prof_out + gridDim.x * 16 + 3 * kProfEvents + prof_g : nullptr;
                 if ((t + 1) * NT <= t_cnt) {
-                    if (kf.sh == 0) process_group<false, true, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane);
-                    else process_group<false, false, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane);
+                    if (kf.sh == 0)
+                        process_group<false, true, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane, ev3, prof_base);
+                    else
+                        process_group<false, false, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane, ev3, prof_base);
                 } else {
-                    process_group<true, false, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane);
+                    process_group<true, false, MODE>(sk, taddr, t, t_cnt, colbase, my_slots, kf, empty, lane, ev3, prof_base);
                 }
+                SFM_PROF_ADD(10);
+                if (prof_me) SFM_PROF_EV(4, prof_g);
+                prof_g += 2;
             }
-            if (MODE != 0) {
+            SFM_PROF_T0();
+            if (MODE != 0 || (probe_flags & 64u)) {
                 if (valid && half == 0) out[out_row + row] = make_int4(static_cast<int>(sk.k1), static_cast<int>(sk.k2), na, 0);
                 continue;
             }
@@ -725,6 +785,14 @@ knn2_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                     out[out_row + row] = flagged ? make_int4(kFlagged, kFlagged, 0, 0) : make_int4(i1, i2, d1, d2);
                 }
             }
+            SFM_PROF_ADD(11);
+        }
+        if (PROF && warp == 0 && lane == 0) {
+            prof_out[blockIdx.x * 16 + 8] = clock64() - prof_begin;
+            prof_out[blockIdx.x * 16 + 9] = prof[9];
+            prof_out[blockIdx.x * 16 + 10] = prof[10];
+            prof_out[blockIdx.x * 16 + 11] = prof[11];
+            prof_out[blockIdx.x * 16 + 12] = prof[12];
         }
     }
 
@@ -745,26 +813,135 @@ __global__ void parity_bits_kernel(const int32_t* __restrict__ norms_pad, long l
     if ((threadIdx.x & 31) == 0 && c < pad_total) par_bits[c >> 5] = bal;
 }
 
-template <int MODE>
+template <int MODE, bool PROF>
 cudaError_t launch_ts_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,
                               const uint8_t* d_bias32, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                               const int32_t* d_norms_pad, const uint32_t* d_par_bits, int32_t* d_flags, int force,
                               const KnnTuning& tn, int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid,
-                              cudaStream_t st) {
+                              long long* d_prof, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(knn2_ts_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(knn2_ts_kernel<MODE, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(kSmemBytes));
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    knn2_ts_kernel<MODE><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms,
-                                                            d_norms_pad, d_par_bits, d_flags, force, tn.probe_flags,
-                                                            d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
+    knn2_ts_kernel<MODE, PROF><<<grid, kThreads, kSmemBytes, st>>>(
+        tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms, d_norms_pad, d_par_bits, d_flags, force,
+        tn.probe_flags, tn.wait_ns, tn.epi_wait_ns, d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn), d_prof);
     return cudaGetLastError();
 }
 
+
+// Hand-over latency probe (one CTA): warp 0 issues `n_mma` MMAs (128 x N x 32, A in TMEM) and a
+// tcgen05.commit to `full`; warp 1 waits for it, takes a time stamp and arrives on `empty`; warp 0 waits
+// for that and takes a time stamp.  out[0] = mean cycles issue start -> issue done (commit issued),
+// out[1] = issue start -> warp 1 past its wait, out[2] = warp 1's arrive -> warp 0 past its wait,
+// out[3] = same-thread variant: issue start -> warp 0 itself past a wait on `full` (iters rounds each).
+template <int N>
+__global__ void __launch_bounds__(64, 1) handover_probe_kernel(int iters, int n_mma, int trail, long long* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    uint8_t* sb = base;   // 256 rows x 128 B of B (contents irrelevant)
+    uint64_t* full = reinterpret_cast<uint64_t*>(base + 256 * 128);
+    uint64_t* empty = full + 1;
+    uint32_t* slot = reinterpret_cast<uint32_t*>(empty + 1);
+    volatile long long* ts = reinterpret_cast<volatile long long*>(slot + 4);   // [0] seen by warp 1, [1] arrive time
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 256 * 128 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(base)[i] = 0x01010101u;
+    fence_proxy_async();
+    if (threadIdx.x == 0) {
+        mbar_init(full, 1);
+        mbar_init(empty, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) {
+        tmem_alloc(slot, kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *slot;
+    constexpr uint32_t idesc = make_idesc_u8(128, N);
+    constexpr uint32_t idesc_t = make_idesc_u8(128, 128);
+    const uint64_t bd = make_kmajor_sw128_desc(smem_u32(sb));
+    long long s_issue = 0, s_seen = 0, s_back = 0, s_self = 0;
+    if (warp == 0) {
+        uint32_t ph = 0;
+        for (int it = 0; it < 2 * iters; ++it) {
+            const bool cross = it < iters;
+            const long long t0 = clock64();
+            if (elect_one()) {
+                for (int k = 0; k < n_mma; ++k)
+                    mma_i8_ts(tmem_base, tmem_base + kAColBase + 8 * (k & 3), bd + uint64_t(k & 3) * 2, idesc, k > 0);
+                mma_commit(full);
+                for (int k = 0; k < trail; ++k)   // later MMAs into another accumulator: must not delay `full`
+                    mma_i8_ts(tmem_base + 128, tmem_base + kAColBase + 8 * (k & 3), bd + uint64_t(k & 3) * 2, idesc_t, k > 0);
+            }
+            __syncwarp();
+            const long long t1 = clock64();
+            if (cross) {
+                mbar_wait(empty, ph);
+                const long long t2 = clock64();
+                s_issue += t1 - t0;
+                s_seen += ts[0] - t0;
+                s_back += t2 - ts[1];
+            } else {
+                mbar_wait(full, ph);
+                const long long t2 = clock64();
+                s_self += t2 - t0;
+                if (lane == 0) mbar_arrive(empty);   // keeps warp 1's phases in step
+                mbar_wait(empty, ph);
+            }
+            ph ^= 1;
+        }
+        if (lane == 0) {
+            out[0] = s_issue / iters;
+            out[1] = s_seen / iters;
+            out[2] = s_back / iters;
+            out[3] = s_self / iters;
+        }
+    } else {
+        uint32_t ph = 0;
+        for (int it = 0; it < 2 * iters; ++it) {
+            if (it < iters) {
+                mbar_wait(full, ph);
+                if (lane == 0) {
+                    ts[0] = clock64();
+                    ts[1] = clock64();
+                    __threadfence_block();
+                    mbar_arrive(empty);
+                }
+                __syncwarp();
+            }
+            ph ^= 1;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
 }  // namespace
+
+int launch_handover_probe(int iters, int n_mma, int tile_n, int trail, long long* d_out, cudaStream_t st, int64_t* launches) {
+    const size_t smem = 256 * 128 + 256 + 1024;
+    cudaError_t e = cudaSuccess;
+    if (tile_n == 256) {
+        e = cudaFuncSetAttribute(handover_probe_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e == cudaSuccess) handover_probe_kernel<256><<<1, 64, smem, st>>>(iters, n_mma, trail, d_out);
+    } else {
+        e = cudaFuncSetAttribute(handover_probe_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e == cudaSuccess) handover_probe_kernel<128><<<1, 64, smem, st>>>(iters, n_mma, trail, d_out);
+    }
+    ++*launches;
+    return static_cast<int>(e != cudaSuccess ? e : cudaGetLastError());
+}
 
 void launch_parity_bits(const int32_t* d_norms_pad, int64_t pad_total, uint32_t* d_par_bits, cudaStream_t st,
                         int64_t* launches) {
@@ -780,21 +957,22 @@ int launch_knn2_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uin
                    const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
                    const uint32_t* d_par_bits, int32_t* d_flags, int variant, int force, const KnnTuning& tn,
                    int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st,
-                   int64_t* launches) {
+                   int64_t* launches, long long* d_prof) {
     if (n_work <= 0) return 0;
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
     int2* fl = reinterpret_cast<int2*>(d_fix_list);
     cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, sizeof(int32_t), st);   // length of this launch's fix list
     if (e != cudaSuccess) return static_cast<int>(e);
+#define SFM_TS_LAUNCH(M, P, F)                                                                                   \
+    launch_ts_variant<M, P>(tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms, d_norms_pad, d_par_bits,    \
+                            d_flags, F, tn, fl, fix_cap, d_knn, grid, d_prof, st)
     if (variant == 1)
-        e = launch_ts_variant<1>(tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms, d_norms_pad, d_par_bits,
-                                 d_flags, 1, tn, fl, fix_cap, d_knn, grid, st);
+        e = d_prof ? SFM_TS_LAUNCH(1, true, 1) : SFM_TS_LAUNCH(1, false, 1);
     else if (variant == 2)
-        e = launch_ts_variant<2>(tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms, d_norms_pad, d_par_bits,
-                                 d_flags, 1, tn, fl, fix_cap, d_knn, grid, st);
+        e = d_prof ? SFM_TS_LAUNCH(2, true, 1) : SFM_TS_LAUNCH(2, false, 1);
     else
-        e = launch_ts_variant<0>(tmap, tmap_x, d_desc, d_bias32, d_work, n_work, d_norms, d_norms_pad, d_par_bits,
-                                 d_flags, force, tn, fl, fix_cap, d_knn, grid, st);
+        e = d_prof ? SFM_TS_LAUNCH(0, true, force) : SFM_TS_LAUNCH(0, false, force);
+#undef SFM_TS_LAUNCH
     ++*launches;
     if (e == cudaSuccess && variant == 0 && !(tn.probe_flags & 4u))   // (probe bit 2: main kernel alone)
         return launch_knn_fix(d_work, n_work, d_desc, d_norms, d_flags, d_fix_list, fix_cap, d_knn, num_sms, st,

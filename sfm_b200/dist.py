@@ -109,17 +109,81 @@ def gather_to_root(t: torch.Tensor, group=None):
     return torch.cat(parts)
 
 
+PER_PAIR_KEYS = ("pairs", "status", "count", "metrics", "F", "kept")
+
+
+def _pack_bytes(tensors):
+    """Concatenate tensors as bytes, every piece padded to 16 bytes (so each can be viewed back)."""
+    pieces = []
+    for t in tensors:
+        b = t.contiguous().view(torch.uint8).reshape(-1)
+        pad = (-b.numel()) % 16
+        pieces.append(b)
+        if pad:
+            pieces.append(torch.zeros(pad, dtype=torch.uint8, device=b.device))
+    return torch.cat(pieces) if pieces else torch.zeros(0, dtype=torch.uint8)
+
+
+def _piece_bytes(n_rows, like):
+    rb = like.element_size() * int(np.prod(like.shape[1:], dtype=np.int64))
+    nb = int(n_rows) * rb
+    return nb, nb + (-nb) % 16
+
+
 def gather_batch_results(local: dict, group=None):
     """local: dict of tensors for this rank's pair range -- per-pair tensors
     (first dim = local pair count) under keys 'pairs','status','count','metrics',
     'F','kept' (number of dense entries per pair) and dense tensors under
-    'dense' (dict).  Rank 0 gets the same structure for ALL pairs, in pair order."""
-    out = {}
-    for k in ("pairs", "status", "count", "metrics", "F", "kept"):
-        out[k] = gather_to_root(local[k], group)
-    out["dense"] = {k: gather_to_root(v, group) for k, v in sorted(local["dense"].items())}
-    if dist.get_rank(group) != 0:
+    'dense' (dict).  Rank 0 gets the same structure for ALL pairs, in pair order.
+
+    One small all-gather of (pairs, dense entries) per rank sizes everything; then every rank
+    sends ONE packed byte buffer to rank 0 and rank 0 posts one receive per rank, all in one
+    batch (NCCL: a single group of send/recv) -- no padding to the largest rank, one host
+    synchronisation (the count vector)."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dense_keys = sorted(local["dense"])
+    tensors = [local[k] for k in PER_PAIR_KEYS] + [local["dense"][k] for k in dense_keys]
+    dev = local["status"].device
+    n_dense = int(local["dense"][dense_keys[0]].shape[0]) if dense_keys else 0
+    cnt = torch.tensor([int(local["status"].shape[0]), n_dense], dtype=torch.int64, device=dev)
+    all_cnt = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(all_cnt, cnt, group=group)
+    all_cnt = torch.stack(all_cnt).cpu().numpy()
+
+    def sizes(r):
+        out = []
+        for i, t in enumerate(tensors):
+            out.append(_piece_bytes(all_cnt[r, 0] if i < len(PER_PAIR_KEYS) else all_cnt[r, 1], t))
+        return out
+
+    ops, rbufs = [], {}
+    if rank == 0:
+        for r in range(1, world):
+            total = sum(padded for _, padded in sizes(r))
+            rbufs[r] = torch.empty(total, dtype=torch.uint8, device=dev)
+            if total:
+                ops.append(dist.P2POp(dist.irecv, rbufs[r], r, group))
+    else:
+        buf = _pack_bytes(tensors)
+        if buf.numel():
+            ops.append(dist.P2POp(dist.isend, buf, 0, group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    if rank != 0:
         return None
+    parts = [list(tensors)]
+    for r in range(1, world):
+        o, got = 0, []
+        for i, (t, (nb, padded)) in enumerate(zip(tensors, sizes(r))):
+            n_rows = all_cnt[r, 0] if i < len(PER_PAIR_KEYS) else all_cnt[r, 1]
+            got.append(rbufs[r][o:o + nb].view(t.dtype).reshape((int(n_rows),) + tuple(t.shape[1:])))
+            o += padded
+        parts.append(got)
+    out = {}
+    for i, k in enumerate(PER_PAIR_KEYS):
+        out[k] = torch.cat([q[i] for q in parts])
+    out["dense"] = {k: torch.cat([q[len(PER_PAIR_KEYS) + i] for q in parts]) for i, k in enumerate(dense_keys)}
     kept = out["kept"].to(torch.int64)
     off = torch.zeros(kept.numel() + 1, dtype=torch.int64, device=kept.device)
     off[1:] = torch.cumsum(kept, 0)

@@ -65,6 +65,7 @@ class PairEngine:
         self.counts = None
         self._bufs = {}
         self._copy_stream = None     # device -> host copies of match_pairs
+        self._marks = None           # stage_times() profiling events
 
     # ------------------------------------------------------------ image set
     def set_images(self, desc, kps, offsets):
@@ -111,6 +112,33 @@ class PairEngine:
         pairs = np.ascontiguousarray(np.asarray(pairs, np.int32)).reshape(-1, 2)
         return [self._match_chunk(pairs[lo:hi], only_ok) for lo, hi in self._chunks(pairs)]
 
+    def _mark(self, name):
+        """Stage boundary for ``stage_times``: a CUDA event on the current stream (only when profiling)."""
+        if self._marks is not None:
+            ev = self.torch.cuda.Event(enable_timing=True)
+            ev.record(self.torch.cuda.current_stream(self.device))
+            self._marks.append((name, ev))
+
+    def stage_times(self, pairs, only_ok: bool = True) -> dict:
+        """One untimed-by-the-caller pass of ``match_device`` with CUDA events between the stages:
+        {'knn', 'filter', 'ransac', 'pack'} -> milliseconds summed over the chunks, plus 'total'
+        (first to last event) and 'gap' = total - sum (launch gaps, host metadata staging)."""
+        torch = self.torch
+        self._marks = []
+        try:
+            self.match_device(pairs, only_ok)
+            torch.cuda.synchronize(self.device)
+            marks = self._marks
+        finally:
+            self._marks = None
+        out = {}
+        for (_, e0), (name, e1) in zip(marks[:-1], marks[1:]):
+            if name != "begin":
+                out[name] = out.get(name, 0.0) + e0.elapsed_time(e1)
+        out["total"] = marks[0][1].elapsed_time(marks[-1][1])
+        out["gap"] = out["total"] - sum(v for k, v in out.items() if k != "total")
+        return out
+
     def _match_chunk(self, pairs, only_ok: bool = True):
         """One chunk: dict of device tensors (the kNN / match arenas are reusable buffers)."""
         torch, ctx = self.torch, self.ctx
@@ -118,6 +146,7 @@ class PairEngine:
         ro = ctx.query_rows(pairs)
         n = int(ro[-1])
         knn = self._buf("knn", (n, 4), torch.int32)
+        self._mark("begin")
         ctx.knn2(pairs, ro, knn)
         knn_rev = ro_rev = None
         if self.mutual:
@@ -125,12 +154,16 @@ class PairEngine:
             ro_rev = ctx.query_rows(rev)
             knn_rev = self._buf("knn_rev", (int(ro_rev[-1]), 4), torch.int32)
             ctx.knn2(rev, ro_rev, knn_rev)
+        self._mark("knn")
         out = (self._buf("mq", (n,), torch.int32), self._buf("mt", (n,), torch.int32),
                self._buf("md2", (n,), torch.int32), self._buf("count", (P,), torch.int32))
         mq, mt, md2, cnt = ctx.filter_matches(pairs, ro, knn, self.ratio, ro_rev, knn_rev, out=out)
+        self._mark("filter")
         v = ctx.verify_pairs(pairs, ro, mq, mt, cnt, self.params)
+        self._mark("ransac")
         pack_off, dense = ctx.pack_results(ro, cnt, v["status"], only_ok, mq=mq, mt=mt, md2=md2,
                                            mask=v["mask"], sym=v["sym"], pts1=v["pts1"], pts2=v["pts2"])
+        self._mark("pack")
         return dict(pairs=pairs, row_off=ro, knn=knn, count=cnt, status=v["status"], metrics=v["metrics"],
                     F=v["F"], pack_off=pack_off, dense=dense)
 

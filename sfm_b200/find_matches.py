@@ -1,10 +1,14 @@
 """Drop-in ``ImageMatcher`` for the preprocess stage, on the B200 matching path.
 
 Mirrors the reference class (utils/find_matches.py:10-364; exported from
-utils/__init__.py:3) method for method -- same names, argument meaning, return
-types, skip gates, output files and CSV columns -- so ``main.py preprocess``
+utils/__init__.py:3) -- same method names, argument meaning, return types, skip
+gates, output files and CSV columns -- so ``main.py preprocess``
 (main.py:189-213) and the reconstruct / image-graph / export stages run
-unchanged on what it writes.  What differs is where the arithmetic happens:
+unchanged on what it writes.  Not mirrored: ``visualize_features_with_mask`` (:26,
+a debugging plot), and ``visualizations/<pair>_matches.png`` (:293-295) is written
+only when ``write_visualizations`` is set (``--visualize``): drawing a PNG per
+passing pair is host work that no later stage reads.  What differs is where the
+arithmetic happens:
 
   * features are extracted ONCE per image (the reference re-detects both images
     for every pair, :265-266) and uploaded once;
@@ -152,6 +156,44 @@ class ImageMatcher:
         return bool(m["inliers"] >= min_inliers and m["inlier_ratio"] >= min_ratio
                     and m["reprojection_error"] <= max_error and m["well_distributed"])
 
+    def visualize_matches(self, img1, img2, kp1, kp2, matches, geometric_results, save_path):
+        """utils/find_matches.py:216-244: the two images side by side, one line per match coloured by
+        the inlier flag, the inlier count as a caption.  kp1 / kp2: cv2.KeyPoint lists or [n,2] arrays."""
+        import cv2
+        mask = geometric_results["inlier_mask"]
+        met = geometric_results["metrics"]
+        h1, w1 = img1.shape[:2]
+        h2, w2 = img2.shape[:2]
+        canvas = np.zeros((max(h1, h2), w1 + w2, 3), np.uint8)
+        canvas[:h1, :w1] = img1 if img1.ndim == 3 else img1[..., None]
+        canvas[:h2, w1:] = img2 if img2.ndim == 3 else img2[..., None]
+
+        def xy(k, i):
+            pt = k[i].pt if hasattr(k[i], "pt") else k[i]
+            return float(pt[0]), float(pt[1])
+
+        for n, m in enumerate(matches):
+            (x1, y1), (x2, y2) = xy(kp1, m.queryIdx), xy(kp2, m.trainIdx)
+            a, b = (int(x1), int(y1)), (int(x2 + w1), int(y2))
+            colour = (0, 255, 0) if mask[n] else (0, 0, 255)
+            cv2.line(canvas, a, b, colour, 1)
+            cv2.circle(canvas, a, 3, colour, -1)
+            cv2.circle(canvas, b, 3, colour, -1)
+        cv2.putText(canvas, f"Inliers: {met['inliers']}/{len(matches)} ({met['inlier_ratio']:.1%})", (10, 30),
+                    cv2.FONT_HERSHEY_SIMPLEX, 1, (255, 255, 255), 2)
+        cv2.imwrite(str(save_path), canvas)
+
+    def _visualize_pair(self, img1_path, img2_path, pair_name, pts1, pts2, mask):
+        """visualize_matches from the packed results of a passing pair (row m matches row m)."""
+        import cv2
+        img1, img2 = cv2.imread(str(img1_path)), cv2.imread(str(img2_path))
+        if img1 is None or img2 is None:
+            return
+        ms = [SimpleNamespace(queryIdx=i, trainIdx=i) for i in range(len(pts1))]
+        res = {"inlier_mask": mask, "metrics": {"inliers": int(mask.sum()),
+                                                "inlier_ratio": float(mask.sum()) / max(len(mask), 1)}}
+        self.visualize_matches(img1, img2, pts1, pts2, ms, res, self.viz_dir / f"{pair_name}_matches.png")
+
     # ------------------------------------------------------------------ pairs
     def process_image_pair(self, img1_path, img2_path, pair_name, mask=False):
         """utils/find_matches.py:246-310 for one pair: dict (CSV row) or None on a skip gate."""
@@ -191,11 +233,18 @@ class ImageMatcher:
         np.savez(self.matches_dir / f"{pair_name}_matches.npz", queryIdx=q.astype(np.int64),
                  trainIdx=t.astype(np.int64), distance=dist.astype(np.float64), inlier_mask=inlier_mask)
 
+    def _write_pair(self, names_p, pair_args, viz):
+        self._save_pair_arrays(*pair_args)
+        if viz:
+            self._visualize_pair(names_p[0], names_p[1], pair_args[0], pair_args[1], pair_args[2], pair_args[4])
+
     def _emit(self, res, names):
         """Write the files of every passing pair of a PairBatchResult and build the CSV rows.
         The four files per pair (:312-327) are written by a small thread pool (row N1 of SURVEY 8f:
         at scale the writer, not the GPU, sets the pace; file I/O and zlib release the GIL); all
-        writes have finished when this returns, as in the reference."""
+        writes have finished when this returns, as in the reference.  A pair whose files cannot be
+        written is logged and loses its row -- that pair only, as the reference's per-pair
+        ``except`` does (:348-350)."""
         rows, jobs = [], []
         pool = None
         if self.writer_threads > 0:
@@ -210,20 +259,29 @@ class ImageMatcher:
                 m = res.metrics[p]
                 args = (pair_name, res.pts1[sl], res.pts2[sl], res.F[p], mask, res.query_idx[sl],
                         res.train_idx[sl], res.distance(p))
-                if pool is None:
-                    self._save_pair_arrays(*args)
-                else:
-                    jobs.append(pool.submit(self._save_pair_arrays, *args))
                 n = int(m["total_matches"])
-                rows.append({
+                row = {
                     "pair_name": pair_name, "img1": Path(img1_path).name, "img2": Path(img2_path).name,
                     "num_matches": n, "num_inliers": np.int64(mask.sum()),
                     "inlier_ratio": np.float64(mask.sum()) / np.float64(n),               # np.mean(bool), :193
                     "reprojection_error": np.float32(m["reprojection_error"]),
                     "well_distributed": bool(m["well_distributed"]),
-                })
-            for j in jobs:
-                j.result()                          # re-raises a writer's exception
+                }
+                if pool is None:
+                    try:
+                        self._write_pair((img1_path, img2_path), args, self.write_visualizations)
+                        rows.append(row)
+                    except Exception as e:
+                        logging.error(f"Error processing pair {pair_name}: {e}")
+                else:
+                    jobs.append((pool.submit(self._write_pair, (img1_path, img2_path), args,
+                                             self.write_visualizations), row))
+            for job, row in jobs:
+                try:
+                    job.result()
+                    rows.append(row)
+                except Exception as e:
+                    logging.error(f"Error processing pair {row['pair_name']}: {e}")
         finally:
             if pool is not None:
                 pool.shutdown(wait=True)
@@ -250,9 +308,29 @@ class ImageMatcher:
                 logging.error(f"Error processing image {i}: {e}")
         return feats
 
+    @staticmethod
+    def _valid_features(feats):
+        """Drop images whose descriptors the GPU path cannot take (not [n,128] integer values 0..255):
+        logged per image, only their pairs are lost (the reference loses one pair at a time, :348-350)."""
+        ok = {}
+        for i, (path, kps, desc) in feats.items():
+            d = np.asarray(desc)
+            try:
+                if d.size and (d.ndim != 2 or d.shape[1] != 128):
+                    raise ValueError(f"descriptors must be [n,128], got {d.shape}")
+                if d.size and not np.array_equal(d.astype(np.uint8).astype(d.dtype), d):
+                    raise ValueError("descriptors must be integer-valued in 0..255 (SIFT)")
+                if len(np.asarray(kps).reshape(-1, 2)) != len(d):
+                    raise ValueError("keypoints and descriptors differ in length")
+                ok[i] = (path, kps, desc)
+            except Exception as e:
+                logging.error(f"Error processing image {i}: {e}")
+        return ok
+
     def process_features(self, feats, start_idx, end_idx):
         """The pair loop of process_image_range (:331-350) over in-memory features: every pair
         i<j of the inclusive range whose two images exist, as ONE batch on the GPU."""
+        feats = self._valid_features(feats)
         ids = sorted(feats)
         pos = {i: n for n, i in enumerate(ids)}
         names, pairs = [], []
@@ -295,18 +373,16 @@ class ImageMatcher:
             torch.cuda.set_device(self.device)
         ids = [i for i in range(start_idx, end_idx + 1) if feat.find_image(self.image_dir, i) is not None]
         b0, b1 = D.image_blocks(len(ids), world)[rank]
-        mine = self.collect_features(start_idx, end_idx, mask, ids=ids[b0:b1])
+        mine = self._valid_features(self.collect_features(start_idx, end_idx, mask, ids=ids[b0:b1]))
         ok = D.all_gather_objects(sorted(mine))                    # an image that failed is absent everywhere
         ids = [i for part in ok for i in part]
         my_ids = ok[rank]
-        for i in my_ids:
-            d = mine[i][2]
-            if len(d) and not np.array_equal(d.astype(np.uint8).astype(d.dtype), d):
-                raise ValueError("descriptors must be integer-valued in 0..255 (SIFT)")
         eng = self._get_engine()
         dev = eng.ctx.device
-        ld = np.concatenate([mine[i][2].astype(np.uint8).reshape(-1, 128) for i in my_ids] or [np.zeros((0, 128), np.uint8)])
-        lk = np.concatenate([np.asarray(mine[i][1], np.float32).reshape(-1, 2) for i in my_ids] or [np.zeros((0, 2), np.float32)])
+        ld = np.concatenate([np.asarray(mine[i][2]).astype(np.uint8).reshape(-1, 128) for i in my_ids]
+                            or [np.zeros((0, 128), np.uint8)])
+        lk = np.concatenate([np.asarray(mine[i][1], np.float32).reshape(-1, 2) for i in my_ids]
+                            or [np.zeros((0, 2), np.float32)])
         desc, kps, off = D.replicate_images(torch.from_numpy(ld).to(dev), torch.from_numpy(lk).to(dev),
                                             [len(mine[i][2]) for i in my_ids])
         pos = {i: n for n, i in enumerate(ids)}
@@ -317,7 +393,7 @@ class ImageMatcher:
                 if i in pos and j in pos:
                     names.append((paths[i], paths[j], f"pair_{i}_{j}"))
                     pairs.append((pos[i], pos[j]))
-        rows = []
+        rows, err = [], None
         if pairs:
             pairs = np.array(pairs, np.int32)
             lo, hi = D.partition_pairs(pairs, np.diff(off), world)[rank]
@@ -328,13 +404,18 @@ class ImageMatcher:
                     self.last_batch = res
                     self.last_names = names[lo:hi]
                     rows = self._emit(res, names[lo:hi])
-            except L.SfmError:
-                raise
-            except Exception as e:
-                logging.error(f"Error processing pairs: {e}")
-        rows = D.gather_rows(rows)
-        if rows is not None:
-            self.results.extend(rows)
+            except Exception as e:                                  # raised on every rank AFTER the collective
+                err = e
+                logging.error(f"Error processing pairs on rank {rank}: {e}")
+        # the rows and a failure flag travel together: no rank is left waiting in a collective
+        parts = D.all_gather_objects((rows, None if err is None else (type(err).__name__, str(err))))
+        fatal = [(r, e) for r, (_, e) in enumerate(parts) if e is not None and e[0] == "SfmError"]
+        if isinstance(err, L.SfmError):
+            raise err
+        if fatal:
+            raise L.SfmError(f"rank {fatal[0][0]} failed: {fatal[0][1][1]}")
+        if rank == 0:
+            self.results.extend(r for part, _ in parts for r in part)
 
     def save_results(self, output_csv):
         """utils/find_matches.py:352-364 (raises KeyError with zero rows, as the reference does)."""
@@ -370,7 +451,8 @@ def _verification_dict(m, mask, sym):
     }
 
 
-def run_preprocessing(data_dir, start_idx=0, end_idx=35, mask=None, device=None) -> bool:
+def run_preprocessing(data_dir, start_idx=0, end_idx=35, mask=None, device=None, mutual=False,
+                      visualize=False) -> bool:
     """``main.py preprocess`` (main.py:189-213): returns the stage's bool.  Under ``torchrun`` the
     process group is joined (NCCL) and the GPU is the local rank's."""
     import os
@@ -383,7 +465,7 @@ def run_preprocessing(data_dir, start_idx=0, end_idx=35, mask=None, device=None)
             torch.cuda.set_device(device)
             dist.init_process_group("nccl", device_id=torch.device("cuda", device))
     try:
-        matcher = ImageMatcher(data_dir, device=device)
+        matcher = ImageMatcher(data_dir, device=device, mutual=mutual, write_visualizations=visualize)
         matcher.process_image_range(start_idx, end_idx, mask)
         matcher.save_results(Path(data_dir) / "matching_results.csv")
         return True

@@ -14,6 +14,8 @@ from sfm_b200 import lib as L, synth  # noqa: E402
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 n_desc = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
 modes = [int(m) for m in sys.argv[3].split(",")] if len(sys.argv) > 3 else [5, 8, 6, 10, 7, 11, 5, 8]
+waits = [tuple(int(x) for x in w.split(":")) for w in sys.argv[4].split(",")] if len(sys.argv) > 4 else [(0, 0)]
+pflags = [int(x) for x in sys.argv[5].split(",")] if len(sys.argv) > 5 else [0]
 s = synth.make_image_set(n_img, n_desc, seed=synth.BASE_SEED + 1, device="cuda", tie_frac=0.01)
 ctx = L.Context(0)
 ctx.set_images(s.desc, s.kps, s.offsets.numpy())
@@ -23,8 +25,10 @@ buf = ctx.empty((int(ro[-1]), 4), torch.int32)
 ops = 256.0 * n_desc * n_desc * len(pairs)
 out = {"pairs": len(pairs), "n_desc": n_desc}
 ref = None
-for mode in modes:
+for mode, (w_ns, e_ns), pf in [(m, w, f) for m in modes for w in waits for f in pflags]:
     ctx.set_knn_mode(mode)
+    ctx.set_knn_probe_flags(pf)
+    ctx.set_knn_waits(w_ns, e_ns)
     ctx.knn2(pairs, ro, buf)
     torch.cuda.synchronize()
     ts = []
@@ -35,8 +39,8 @@ for mode in modes:
         e1.record()
         torch.cuda.synchronize()
         ts.append(round(ops / (e0.elapsed_time(e1) * 1e-3) / 1e12, 1))
-    out.setdefault(f"mode{mode}_tops", []).append(ts)
-    if mode in (5, 8):
+    out.setdefault(f"mode{mode}_w{w_ns}_e{e_ns}_pf{pf}_tops", []).append(ts)
+    if mode in (5, 8) and pf == 0:
         got = buf.clone()
         if ref is None:
             ref = got
@@ -44,5 +48,7 @@ for mode in modes:
         out[f"brute_rows_mode{mode}"] = ctx.brute_rows()
     print(json.dumps(out), flush=True)
 ctx.set_knn_mode(0)
+ctx.set_knn_waits(0, 0)
+ctx.set_knn_probe_flags(0)
 Path("gpurun_out").mkdir(exist_ok=True)
 Path(f"gpurun_out/r02_ab_knn_{n_img}x{n_desc}.json").write_text(json.dumps(out, indent=1))
