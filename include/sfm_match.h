@@ -239,6 +239,13 @@ SFM_API int sfm_debug_wide_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int3
  * (sfm_b200/csrc/knn_ts.cu: query rows written to tensor memory with tcgen05.st, tcgen05.mma with
  * the A operand in TMEM), written to d_out i32 [128,128]. */
 SFM_API int sfm_debug_ts_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+/* Debug: the same folded accumulators for a 256 x 128 tile through the CTA-pair path
+ * (sfm_b200/csrc/knn_pair.cu: a cluster of two CTAs, tcgen05.mma.cta_group::2 with M = 256, N = 128,
+ * each CTA staging its 128 query rows and 64 of the 128 train rows), written to d_out i32 [256,128]. */
+SFM_API int sfm_debug_pair_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
+/* Cycle counters the pair kernel's first epilogue warp leaves behind when probe flag 512 is set
+ * (main loop, resolve, recompute, merge + write, recomputed rows, work items, -, -). */
+SFM_API int sfm_debug_pair_counters(sfm_ctx* ctx, int64_t* h_out8, void* stream);
 /* Issue-rate probe of 128 x tile_n x 32 u8 MMAs (tile_n = 64, 96, 128, 192 or 256) in groups of
  * five, accumulators rotating over 384 / tile_n TMEM stages, no data movement.  ts != 0: A operand
  * in tensor memory, else in shared memory; commit != 0: one tcgen05.commit per group.

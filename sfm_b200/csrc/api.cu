@@ -102,6 +102,7 @@ struct sfm_ctx {
     std::vector<int64_t> h_off, h_pad, h_x;
     CUtensorMap tmap, tmap_x;
     CUtensorMap tmap_x32, tmap_ax32;   // wide kNN variant: fold operands as 32-byte rows (knn_wide.cu)
+    CUtensorMap tmap_b64, tmap_x64;    // pair kNN variant: 64-row boxes of the descriptor / fold operand rows (knn_pair.cu)
     DevBuf<uint8_t> d_bias32;
     DevBuf<int32_t> d_fix_list;  // (work item, row) of the rows the wide kNN kernel leaves to its fix-up pass
     static constexpr int32_t kFixCap = 1 << 18;
@@ -364,6 +365,16 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
                             estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (bias32) failed: CUresult %d", int(r));
+        const cuuint32_t hbox[2] = {SFM_DESC_DIM, 64};
+        const cuuint32_t hxbox[2] = {32, 64};
+        r = ctx->encode(&ctx->tmap_b64, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(d_desc), gdim, gstride,
+                        hbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = ctx->encode(&ctx->tmap_x64, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_bias32.p, wdim, wstride, hxbox,
+                            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (64-row boxes) failed: CUresult %d", int(r));
         ctx->have_tmap = true;
     }
     sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, ctx->d_x_off.p, n_images,
@@ -408,11 +419,16 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
-    if (km >= 8 && ctx->knn_prof) {
+    if (km >= 8 && km < 12 && ctx->knn_prof) {
         SFM_CUDA(ctx, ctx->d_prof.reserve(static_cast<size_t>(ctx->num_sms) * 16 + 5 * 4096));
         SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_prof.p, 0, sizeof(long long) * (ctx->num_sms * 16 + 5 * 4096), st));
     }
-    if (km >= 8)
+    if (km >= 12)
+        r = sfm::launch_knn2_pair(ctx->tmap, ctx->tmap_b64, ctx->tmap_x64, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p,
+                                  n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
+                                  km - 12, ctx->knn_mode != 0, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
+                                  ctx->num_sms, st, &ctx->launches);
+    else if (km >= 8)
         r = sfm::launch_knn2_ts(ctx->tmap, ctx->tmap_ax32, ctx->d_desc, ctx->d_bias32.p, ctx->d_work.p, n_work,
                                 ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
                                 km == 10 ? 1 : (km == 11 ? 2 : 0), ctx->knn_mode != 0, ctx->knn_tuning,
@@ -423,7 +439,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
                                   ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
                                   ctx->num_sms, st, &ctx->launches);
-    const bool folded_auto = (km == 5 || km == 8) && ctx->knn_mode == 0;
+    const bool folded_auto = (km == 5 || km == 8 || km == 12) && ctx->knn_mode == 0;
     if (!r && (km < 5 || folded_auto))
         r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                              ctx->d_norms_pad.p, ctx->d_flags.p, folded_auto ? 9 : km, ctx->knn_tuning, d_knn,
@@ -726,6 +742,30 @@ int sfm_debug_ts_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out
     return 0;
 }
 
+int sfm_debug_pair_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream) {
+    if (!ctx) return 1;
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
+    if (!d_out) return ctx->fail("d_out is NULL");
+    if (q_row < 0 || t_row < 0 || q_row >= ctx->total_rows || t_row >= ctx->total_rows)
+        return ctx->fail("tile rows out of range");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    int r = sfm::launch_debug_pair(ctx->tmap, ctx->tmap_b64, ctx->tmap_x64, ctx->tmap_ax32, static_cast<int32_t>(q_row),
+                                   static_cast<int32_t>(t_row), d_out, static_cast<cudaStream_t>(stream),
+                                   &ctx->launches);
+    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    return 0;
+}
+
+int sfm_debug_pair_counters(sfm_ctx* ctx, int64_t* h_out8, void* stream) {
+    if (!ctx || !h_out8) return 1;
+    if (!ctx->d_fix_list.p) return ctx->fail("no descriptors registered");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, cudaMemcpyAsync(h_out8, ctx->d_fix_list.p + sfm_ctx::kFixCap, 8 * sizeof(int64_t),
+                                  cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+    SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 int sfm_debug_ts_rate_probe(sfm_ctx* ctx, int32_t groups, int32_t tile_n, int32_t ts, int32_t commit, float* ms,
                             double* ops, void* stream) {
     if (!ctx) return 1;
@@ -802,7 +842,7 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (mode < 0 || mode > 11 || mode == 9) return ctx->fail("knn mode must be 0..8, 10 or 11");
+    if (mode < 0 || mode > 14 || mode == 9) return ctx->fail("knn mode must be 0..8 or 10..14");
     ctx->knn_mode = mode;
     return 0;
 }

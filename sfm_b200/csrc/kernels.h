@@ -72,6 +72,17 @@ int launch_knn2_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uin
                    const uint32_t* d_par_bits, int32_t* d_flags, int variant, int force, const struct KnnTuning& tn,
                    int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st,
                    int64_t* launches, long long* d_prof = nullptr);
+// ---- knn_pair.cu (cta_group::2: a cluster of two CTAs per 256 query rows, four 128-column accumulator stages)
+// tmap_a = descriptor rows in 128-row boxes, tmap_b = the same array in 64-row boxes, tmap_x = fold operand rows
+// (32 B) in 64-row boxes, tmap_ax = the same array in a 128-row box (constant rows).
+int launch_knn2_pair(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_x,
+                     const CUtensorMap& tmap_ax, const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work,
+                     const int32_t* d_norms, const int32_t* d_norms_pad, const uint32_t* d_par_bits,
+                     int32_t* d_flags, int variant, int force, const struct KnnTuning& tn, int32_t* d_fix_list,
+                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
+int launch_debug_pair(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_x,
+                      const CUtensorMap& tmap_ax, int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st,
+                      int64_t* launches);
 int launch_handover_probe(int iters, int n_mma, int tile_n, int trail, long long* d_out, cudaStream_t st, int64_t* launches);
 int launch_ts_rate_probe(int groups, int tile_n, int ts, int commit, int num_sms, cudaStream_t st,
                          int64_t* launches);

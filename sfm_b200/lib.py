@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_ts_rate_probe", "sfm_debug_knn_profile", "sfm_debug_knn_profile_events", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_knn_profile", "sfm_debug_knn_profile_events", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -94,6 +94,8 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_debug_fold_tile.argtypes = [vp, i64, i32, i32, vp, vp]
     lib.sfm_debug_wide_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_ts_tile.argtypes = [vp, i64, i64, vp, vp]
+    lib.sfm_debug_pair_tile.argtypes = [vp, i64, i64, vp, vp]
+    lib.sfm_debug_pair_counters.argtypes = [vp, C.POINTER(i64), vp]
     lib.sfm_debug_ts_rate_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_set_knn_mode.argtypes = [vp, i32]
     lib.sfm_debug_knn_profile.argtypes = [vp, i32, C.POINTER(i64), vp]
@@ -386,6 +388,17 @@ class Context:
         self._check(self.lib.sfm_debug_ts_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
                                                self._stream()))
         return out
+
+    def debug_pair_tile(self, q_row, t_row):
+        out = self.empty((256, 128), self.torch.int32)
+        self._check(self.lib.sfm_debug_pair_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
+                                                 self._stream()))
+        return out
+
+    def pair_counters(self):
+        buf = (C.c_int64 * 8)()
+        self._check(self.lib.sfm_debug_pair_counters(self.h, buf, self._stream()))
+        return list(buf)
 
     def ts_rate_probe(self, tile_n, ts=1, commit=0, groups=8192):
         """-> TOP/s of groups of five 128 x tile_n x 32 u8 MMAs (A in TMEM when ts, else shared memory)."""
