@@ -63,11 +63,14 @@ typedef struct sfm_verify_params {
     double min_ratio;       /* 0.3 */
     double max_error;       /* 2.0 */
     double min_spread;      /* 20    utils/find_matches.py:185 */
-    int32_t score_mode;     /* bit 0: hypotheses scored by the symmetric epipolar error instead of
+    int32_t score_mode;     /* 3.  bit 0: hypotheses scored by the symmetric epipolar error instead of
                                Sampson; bit 1: the inlier refits use the symmetric error (the
-                               measure geometric_verification applies, :165-172) */
-    int32_t min_work;       /* 262144: floor on hypotheses x matches before the adaptive stop may
-                               end the search (at most 4096 hypotheses); 0 disables */
+                               measure geometric_verification applies, :165-172).  Sampson scoring
+                               (0 / 2) leaves the SURVEY 8c envelope on the 148 golden pairs (4-6
+                               inlier-bound failures per seed, tests/ransac_tune.py) and is no faster */
+    int32_t min_work;       /* 65536: floor on hypotheses x matches before the adaptive stop may end the
+                               search, for pairs of 15..256 matches (tapering to none at 384; at most
+                               4096 hypotheses); 0 disables */
 } sfm_verify_params;
 
 /* Per-pair metrics, the dict returned by ImageMatcher.geometric_verification

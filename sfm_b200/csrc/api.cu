@@ -203,7 +203,7 @@ void sfm_default_params(sfm_verify_params* p) {
     p->max_error = 2.0;
     p->min_spread = 20.0;
     p->score_mode = 3;
-    p->min_work = 1 << 18;
+    p->min_work = 1 << 16;
 }
 
 const char* sfm_last_error(sfm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -391,7 +391,10 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
     if (n_pairs == 0) return 0;
-    if (!h_row_off || !d_knn) return ctx->fail("NULL argument");
+    if (!h_row_off) return ctx->fail("NULL argument");
+    // an image set whose images are all empty has no rows and no tensor map: every pair is then a
+    // "too few features" skip of the reference (utils/find_matches.py:268), not an error
+    if (ctx->n_images > 0 && ctx->total_rows == 0) return 0;
     if (!ctx->have_tmap) return ctx->fail("no descriptors registered (sfm_set_images)");
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
     // work-item prefix: ceil(n_query / 256) blocks per pair
@@ -405,6 +408,8 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
         ctx->h_meta[p + 1] = ctx->h_meta[p] + (nq + SFM_QBLOCK - 1) / SFM_QBLOCK;
     }
     const int64_t n_work = ctx->h_meta[n_pairs];
+    if (n_work == 0) return 0;   // every query image of the list is empty
+    if (!d_knn) return ctx->fail("NULL argument");
     const int64_t *d_prefix, *d_row;
     if (stage_meta(ctx, h_pairs, n_pairs, ctx->h_meta.data(), h_row_off, nullptr, st, &d_prefix, &d_row,
                    nullptr))
@@ -423,7 +428,11 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
         SFM_CUDA(ctx, ctx->d_prof.reserve(static_cast<size_t>(ctx->num_sms) * 16 + 5 * 4096));
         SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_prof.p, 0, sizeof(long long) * (ctx->num_sms * 16 + 5 * 4096), st));
     }
-    if (km >= 12)
+    if (km == 15)   // wide kernel with the warp-uniform skip of the unit bookkeeping (A/B against mode 5)
+        r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
+                                  ctx->d_norms_pad.p, ctx->d_flags.p, 3, 1, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap,
+                                  d_knn, ctx->num_sms, st, &ctx->launches);
+    else if (km >= 12)
         r = sfm::launch_knn2_pair(ctx->tmap, ctx->tmap_b64, ctx->tmap_x64, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p,
                                   n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
                                   km - 12, ctx->knn_mode != 0, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
@@ -842,7 +851,7 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (mode < 0 || mode > 14 || mode == 9) return ctx->fail("knn mode must be 0..8 or 10..14");
+    if (mode < 0 || mode > 15 || mode == 9) return ctx->fail("knn mode must be 0..8 or 10..15");
     ctx->knn_mode = mode;
     return 0;
 }

@@ -220,8 +220,20 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
             }
             const uint64_t key = pair_ids ? rc::pair_key(prm.seed, pair_ids[2 * p], pair_ids[2 * p + 1])
                                           : rc::pair_key(prm.seed, static_cast<uint32_t>(p), 0xffffffffu);
-            // small pairs are cheap: never stop before hypotheses x matches >= min_work
-            int floor_h = prm.min_work > 0 ? ((prm.min_work + m - 1) / m + 255) & ~255 : 0;
+            // Small pairs are cheap and their first rounds easily miss a good model: never stop before
+            // hypotheses x matches >= min_work.  The floor is for bunny-scale pairs (m <= 256, where the 148
+            // golden pairs need it to stay inside the SURVEY 8c envelope: with min_work = 2^16 no bound or
+            // Jaccard failure and at most 2 boundary gate flips over three seeds, the same as with 2^18, while
+            // without it up to 6 flips and a Jaccard failure -- tests/ransac_tune.py); it tapers to nothing at m = 384:
+            // on 147 reference-passing synthetic 8k-config pairs (median 412 matches) the envelope against
+            // cv2.findFundamentalMat is the same with and without it (Jaccard median 0.970, p10 0.908, no
+            // bound failure, no gate flip; tests/ransac_synth_envelope.py), at 0.65 instead of 1.55 us per pair.
+            // (Fewer matches than the inlier gate asks for cannot pass it whatever F is: no floor either.)
+            int floor_h = 0;
+            if (prm.min_work > 0 && m < 384 && m >= prm.min_inliers) {
+                const long long w = m <= 256 ? prm.min_work : static_cast<long long>(prm.min_work) * (384 - m) / 128;
+                floor_h = static_cast<int>(((w + m - 1) / m + 255) & ~255ll);
+            }
             floor_h = floor_h > 4096 ? 4096 : floor_h;
             const int limit = max_iters > floor_h ? max_iters : floor_h;
             if (threadIdx.x == 0) {

@@ -179,9 +179,16 @@ class Context:
         torch = self.torch
         if t.device != self.device or t.dtype != dtype or not t.is_contiguous():
             raise SfmError(f"expected contiguous {dtype} tensor on {self.device}")
+        if t.numel() == 0:
+            # torch reports a NULL data pointer for an empty tensor; the C ABI takes NULL for "argument
+            # missing", so a legitimately empty array (images without features) is given real storage
+            if getattr(self, "_nil", None) is None:
+                self._nil = torch.zeros(64, dtype=torch.uint8, device=self.device)
+            return C.c_void_p(self._nil.data_ptr())
         return C.c_void_p(t.data_ptr())
 
     def empty(self, shape, dtype):
+        shape = tuple(int(x) for x in (shape if isinstance(shape, (tuple, list)) else (shape,)))
         return self.torch.empty(shape, dtype=dtype, device=self.device)
 
     @property
@@ -199,8 +206,8 @@ class Context:
             raise SfmError("offsets[-1] must equal the number of descriptor rows")
         if kps is not None and tuple(kps.shape) != (desc.shape[0], 2):
             raise SfmError("kps must be [rows, 2] float32")
-        dptr = self._dev(desc, torch.uint8) if desc.numel() else C.c_void_p(0)
-        kptr = self._dev(kps, torch.float32) if kps is not None and kps.numel() else C.c_void_p(0)
+        dptr = self._dev(desc, torch.uint8)              # (an empty set still passes real storage)
+        kptr = self._dev(kps, torch.float32) if kps is not None else C.c_void_p(0)
         self._check(self.lib.sfm_set_images(self.h, dptr, kptr, _h(off), len(off) - 1, self._stream()))
         self._keep = (desc, kps)
         self.offsets = off

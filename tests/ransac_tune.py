@@ -20,7 +20,7 @@ def main():
     p2 = torch.from_numpy(z["pts2"]).cuda()
     P = len(off) - 1
     import itertools
-    for thr, lo, mode, seed, mi in itertools.product((3.0,), (2,), (3,), (0x5F3759DF2024, 1, 2, 3, 4, 5), (1 << 16, 1 << 18)):
+    for thr, lo, mode, seed, mi in itertools.product((3.0,), (2, 4, 8), (3,), (0x5F3759DF2024, 1, 2), (1 << 18, 1 << 16, 1 << 14, 0)):
         if True:
             prm = L.default_params(ransac_thresh=thr, lo_iters=lo, score_mode=mode, seed=seed, min_work=mi)
             o = ctx.ransac_points(off, p1, p2, prm)
@@ -46,13 +46,11 @@ def main():
                                   round(float(met["reprojection_error"][k]), 3), int(met["well_distributed"][k]),
                                   round(float(min(z["pts1"][s][mask[s]].std(0).min(), z["pts2"][s][mask[s]].std(0).min())), 2)))
             jac = np.array(jac)
-            print(f"seed {seed} mi {mi}: jac med {np.median(jac):.3f} p10 {np.percentile(jac, 10):.3f} min {jac.min():.3f} | "
+            print(f"lo {lo} seed {seed & 0xff} mi {mi}: jac med {np.median(jac):.3f} p10 {np.percentile(jac, 10):.3f} min {jac.min():.3f} | "
                   f"dI med {np.median(dI):+.0f} min {min(dI)} max {max(dI)} | iters med {np.median(met['ransac_iters']):.0f} | "
                   f"bound-fails {len(bad1)} jac-fails {len(badj)} flips {len(flips)}")
-            if True:
-                print("  bound fails:", bad1)
-                print("  jac fails:", badj)
-                print("  flips:", flips)
+            if bad1 or badj:
+                print(f"    bound fails {bad1}; jac fails {badj}")
 
 
 if __name__ == "__main__":
