@@ -64,7 +64,7 @@ def config_of(wl, mutual):
     """The `config` object: identical in the B200 arm and the reference arm."""
     from sfm_b200 import synth
     return {"workload": wl["name"], "n_images": wl["n_images"], "n_desc": wl["n_desc"], "pairs": wl["pairs"],
-            "ratio": RATIO, "mutual_nn": bool(mutual), "seed": synth.BASE_SEED + wl["seed_off"],
+            "ratio": RATIO, "mutual_nn": {0: False, 1: "sparse reverse pass", 2: "full reverse pass"}[int(mutual)], "seed": synth.BASE_SEED + wl["seed_off"],
             "tie_frac": TIE_FRAC, "generator": "numpy default_rng on the host, image i from (seed, 1 + i)"}
 
 
@@ -87,7 +87,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
                  "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -228,6 +228,10 @@ def parity_sample(eng, L, host_desc, host_kps, off, pairs, n_check=8, seed=11):
     for p, (i, j) in enumerate(pairs[pick]):
         a, b = slice(off[i], off[i + 1]), slice(off[j], off[j + 1])
         q, t, d = oknn.match_features_cv2(host_desc[a], host_desc[b], RATIO)
+        if eng.mutual:       # + cv2's own cross-check: (q, t) survives iff BFMatcher(crossCheck=True) keeps it
+            cq, ct = oknn.mutual_nn_cv2(host_desc[a], host_desc[b])
+            keep = np.isin(q * (1 << 32) + t, np.asarray(cq, np.int64) * (1 << 32) + np.asarray(ct, np.int64))
+            q, t, d = q[keep], t[keep], d[keep]
         sl = res.pair_slice(p)
         knn_ok &= bool(np.array_equal(res.query_idx[sl], q) and np.array_equal(res.train_idx[sl], t)
                        and np.array_equal(res.distance(p), d))
@@ -239,7 +243,8 @@ def parity_sample(eng, L, host_desc, host_kps, off, pairs, n_check=8, seed=11):
             n_ver += 1
     return {"pairs": int(len(pick)), "knn_ratio_lists_identical_to_cv2": knn_ok,
             "verification_pairs": n_ver, "verification_identical_given_F": ver_ok,
-            "oracle": "oracle.knn.match_features_cv2 + oracle.fundamental.geometric_verification"}
+            "oracle": "oracle.knn.match_features_cv2" + (" + mutual_nn_cv2 (BFMatcher crossCheck)" if eng.mutual else "")
+                      + " + oracle.fundamental.geometric_verification"}
 
 
 def run_b200(args):
@@ -314,7 +319,7 @@ def run_b200(args):
     pairs = all_pairs(n)
     lo, hi = D.partition_pairs(pairs, counts, world)[rank]
     my_pairs = pairs[lo:hi]
-    eng = PairEngine(local_rank, mutual=bool(args.mutual))
+    eng = PairEngine(local_rank, mutual={0: False, 1: True, 2: "full"}[args.mutual])
     eng.set_images(desc, kps, off)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)               # > 126 MB L2
 
@@ -333,8 +338,12 @@ def run_b200(args):
             e1.record()
         barrier()
         launches = eng.ctx.launches - launches0
-        ms_total = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in ev))
+        my_steps = [e0.elapsed_time(e1) for e0, e1 in ev]
+        ms_total = max_over_ranks(sum(my_steps))
         ms_step = ms_total / args.steps
+        # per-rank view of the same steps (mean, slowest step): a straggling rank or a host-side gap shows here
+        by_rank = [(round(float(np.mean(x)), 3), round(float(np.max(x)), 3))
+                   for x in (D.all_gather_objects(my_steps) if world > 1 else [my_steps])]
         n_ok = sum(int((c["status"] == L.PAIR_OK).sum().item()) for c in chunks)
         n_matches = sum(int(c["count"].sum().item()) for c in chunks)
         hyp_pts = 0.0
@@ -546,6 +555,7 @@ def run_b200(args):
             "run": {"pairs_passing_verification": n_ok, "matches_after_ratio": n_matches,
                     "parallelism": f"pair list cut into {world} contiguous ranges of equal n_i*n_j",
                     "l2": "flushed between steps (256 MiB write)",
+            "ms_per_step_by_rank_mean_max": by_rank,
                     "ransac_hypotheses_x_points_per_sec_rank0": hyp_pts / (ransac_ms * 1e-3) if ransac_ms > 0 else None},
             "comparisons_per_sec": cmp_s, "int8_tops": whole_tops,
             "whole_step_frac_of_nominal_int8": whole_tops / (NOMINAL_INT8_TOPS * world),
@@ -587,7 +597,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="200x8k", choices=sorted(WORKLOADS))
-    ap.add_argument("--mutual", type=int, default=0, help="1: add the mutual-NN check")
+    ap.add_argument("--mutual", type=int, default=0, choices=[0, 1, 2],
+                    help="1: add the mutual-NN check (sparse form: only the surviving matches go back); "
+                         "2: the same by a second exhaustive kNN pass over the reversed pairs")
     ap.add_argument("--target-config", default="auto",
                     help="auto (1000x8k; + 500x32k at 8 GPUs), none, or a comma list of workload keys")
     ap.add_argument("--parity-pairs", type=int, default=8)

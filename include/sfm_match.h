@@ -137,6 +137,19 @@ SFM_API int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_p
                        int32_t* d_count, void* stream);
 
 /* ---- K3 + K4: RANSAC fundamental matrix + geometric verification ------ */
+/* Mutual nearest-neighbour check on match lists that have passed the ratio test (README.md:108 of the
+ * reference, "mutual nearest neighbor check"; the reference's code path has none).  Match i of pair p
+ * = (i, j) is kept iff its query row is the nearest row of image i to its train descriptor (lowest
+ * index on ties, as cv2.BFMatcher(crossCheck=True) decides).  Sparse form: only the train descriptors
+ * of the surviving matches are matched back against image i, not all n_j rows.
+ * h_count: host copy of d_count (the caller fetches it; this is the one synchronisation the check needs).
+ * The lists d_mq / d_mt / d_md2 are compacted in place (ascending query index kept), d_count rewritten.
+ * Fails when a descriptor norm is beyond the folded kernel's range (then use sfm_knn2 on the reversed
+ * pairs + sfm_filter_matches with d_knn_rev). */
+SFM_API int sfm_mutual_filter(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
+                              const int32_t* h_count, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2,
+                              int32_t* d_count, void* stream);
+
 /* Replaces, per pair: the point gather utils/find_matches.py:278-279,
  * cv2.findFundamentalMat(pts1, pts2, FM_RANSAC, 3.0) (:282),
  * geometric_verification (:157-201) and verify_match_quality (:203-214).

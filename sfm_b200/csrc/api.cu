@@ -113,6 +113,15 @@ struct sfm_ctx {
     bool knn_prof = false;
     DevBuf<uint32_t> d_par_bits;   // norm parities of the padded column space, 32 per word (knn_ts.cu)
     DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
+    // sfm_mutual_filter scratch: gathered train descriptors / norms of the surviving matches, their
+    // reverse kNN rows, the per-pair match offsets and the reverse pass's work items
+    DevBuf<uint8_t> d_qdesc;
+    DevBuf<int32_t> d_qnorms, d_knn_rev;
+    DevBuf<int64_t> d_moff;
+    DevBuf<sfm::WorkItem> d_work_rev;
+    std::vector<int64_t> h_moff;
+    std::vector<sfm::WorkItem> h_work_rev;
+    int fold_flag_host = -1;     // flags[0] read back once per image set (-1: not yet)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
     int knn_auto = 5;            // what mode 0 resolves to: 5 = wide fold kernel + generic, 8 = TS kernel + generic
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
@@ -266,6 +275,11 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_flags.release();
     ctx->d_bias.release();
     ctx->d_bias32.release();
+    ctx->d_qdesc.release();
+    ctx->d_qnorms.release();
+    ctx->d_knn_rev.release();
+    ctx->d_moff.release();
+    ctx->d_work_rev.release();
     ctx->d_par_bits.release();
     ctx->d_prof.release();
     ctx->d_fix_list.release();
@@ -298,6 +312,7 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
 
     ctx->d_desc = d_desc;
     ctx->d_kps = d_kps;
+    ctx->fold_flag_host = -1;
     ctx->n_images = n_images;
     ctx->total_rows = total;
     ctx->h_off.assign(h_offsets, h_offsets + n_images + 1);
@@ -477,6 +492,87 @@ int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
                        reinterpret_cast<const int4*>(d_knn), d_row_rev,
                        reinterpret_cast<const int4*>(d_knn_rev), ratio, d_mq, d_mt, d_md2, d_count, st,
                        &ctx->launches);
+    SFM_CUDA(ctx, cudaGetLastError());
+    return 0;
+}
+
+int sfm_mutual_filter(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
+                      const int32_t* h_count, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2, int32_t* d_count,
+                      void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
+    if (n_pairs == 0) return 0;
+    if (!h_row_off || !h_count || !d_mq || !d_mt || !d_md2 || !d_count) return ctx->fail("NULL argument");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    // per-pair offsets of the surviving matches and the work items of the reverse pass: blocks of up to
+    // 256 gathered train descriptors (queries) against every row of the pair's FIRST image
+    ctx->h_moff.resize(static_cast<size_t>(n_pairs) + 1);
+    ctx->h_work_rev.clear();
+    ctx->h_moff[0] = 0;
+    for (int32_t p = 0; p < n_pairs; ++p) {
+        const int32_t qi = h_pairs[2 * p];
+        const int64_t nq = ctx->h_off[qi + 1] - ctx->h_off[qi];
+        const int32_t m = h_count[p];
+        if (m < 0 || m > h_row_off[p + 1] - h_row_off[p])
+            return ctx->fail("h_count[%d] = %d does not fit the pair's rows", p, m);
+        ctx->h_moff[p + 1] = ctx->h_moff[p] + m;
+        for (int32_t b = 0; b < m; b += SFM_QBLOCK) {
+            sfm::WorkItem w;
+            w.q_row = static_cast<int32_t>(ctx->h_moff[p] + b);
+            w.q_cnt = m - b < SFM_QBLOCK ? m - b : SFM_QBLOCK;
+            w.t_row = static_cast<int32_t>(ctx->h_off[qi]);
+            w.t_cnt = static_cast<int32_t>(nq);
+            w.t_pad = static_cast<int32_t>(ctx->h_pad[qi]);
+            w.x_row = static_cast<int32_t>(ctx->h_x[qi]);
+            w.out_row = ctx->h_moff[p] + b;
+            ctx->h_work_rev.push_back(w);
+        }
+    }
+    const int64_t total = ctx->h_moff[n_pairs];
+    if (total == 0) return 0;
+    if (total >= (int64_t(1) << 31) - 512) return ctx->fail("too many matches for one mutual pass");
+    if (!ctx->have_tmap) return ctx->fail("no descriptors registered (sfm_set_images)");
+    if (ctx->fold_flag_host < 0) {   // once per image set (the caller has just synchronised for h_count anyway)
+        int32_t f = 0;
+        SFM_CUDA(ctx, cudaMemcpyAsync(&f, ctx->d_flags.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        SFM_CUDA(ctx, cudaStreamSynchronize(st));
+        ctx->fold_flag_host = f != 0;
+    }
+    if (ctx->fold_flag_host)
+        return ctx->fail("a descriptor norm is beyond the fold range: use the reversed kNN pass for the mutual check");
+    const int64_t q_rows = total + SFM_QBLOCK;   // a block's tensor-memory load may run past the last match
+    SFM_CUDA(ctx, ctx->d_qdesc.reserve(static_cast<size_t>(q_rows) * SFM_DESC_DIM));
+    SFM_CUDA(ctx, ctx->d_qnorms.reserve(static_cast<size_t>(q_rows)));
+    SFM_CUDA(ctx, ctx->d_knn_rev.reserve(static_cast<size_t>(total) * 4));
+    SFM_CUDA(ctx, ctx->d_moff.reserve(static_cast<size_t>(n_pairs) + 1));
+    SFM_CUDA(ctx, ctx->d_work_rev.reserve(ctx->h_work_rev.size()));
+    const int64_t* d_row;
+    if (stage_meta(ctx, h_pairs, n_pairs, nullptr, h_row_off, nullptr, st, nullptr, &d_row, nullptr)) return 1;
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_moff.p, ctx->h_moff.data(), sizeof(int64_t) * (n_pairs + 1), st));
+    SFM_CUDA(ctx, ctx->ring.copy(ctx->d_work_rev.p, ctx->h_work_rev.data(),
+                                 sizeof(sfm::WorkItem) * ctx->h_work_rev.size(), st));
+    CUtensorMap qmap;
+    {
+        const cuuint64_t gdim[2] = {SFM_DESC_DIM, static_cast<cuuint64_t>(q_rows)};
+        const cuuint64_t gstride[1] = {SFM_DESC_DIM};
+        const cuuint32_t box[2] = {SFM_DESC_DIM, SFM_TTILE};
+        const cuuint32_t estr[2] = {1, 1};
+        CUresult r = ctx->encode(&qmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_qdesc.p, gdim, gstride, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (mutual queries) failed: CUresult %d", int(r));
+    }
+    sfm::launch_mutual_gather(ctx->d_pairs.p, n_pairs, ctx->d_img_off.p, d_row, ctx->d_moff.p, d_mt, ctx->d_desc,
+                              ctx->d_norms.p, ctx->d_qdesc.p, ctx->d_qnorms.p, st, &ctx->launches);
+    const sfm::KnnQuery query{&qmap, ctx->d_qdesc.p, ctx->d_qnorms.p};
+    const int r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work_rev.p,
+                                        static_cast<int64_t>(ctx->h_work_rev.size()), ctx->d_norms.p,
+                                        ctx->d_norms_pad.p, ctx->d_flags.p, 0, 0, ctx->knn_tuning, ctx->d_fix_list.p,
+                                        sfm_ctx::kFixCap, ctx->d_knn_rev.p, ctx->num_sms, st, &ctx->launches, &query);
+    if (r) return ctx->fail("mutual kNN launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
+    sfm::launch_mutual_compact(n_pairs, d_row, ctx->d_moff.p, reinterpret_cast<const int4*>(ctx->d_knn_rev.p), d_mq,
+                               d_mt, d_md2, d_count, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
     return 0;
 }

@@ -47,11 +47,20 @@ int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t s
 // ---- knn_wide.cu (N = 256 folded kernel; fold operands as u8 [128 + R, 32])
 void launch_bias32(const int32_t* d_norms, int64_t total_rows, uint8_t* d_bias32, int32_t* d_flags,
                    cudaStream_t st, int64_t* launches);
+// Query rows that are not rows of the registered descriptor array (the mutual check matches the train
+// descriptors of the surviving matches back against the query image): their own tensor map (128-row
+// boxes), descriptor rows and squared norms; WorkItem::q_row indexes THIS array.
+struct KnnQuery {
+    const CUtensorMap* tmap;
+    const uint8_t* desc;
+    const int32_t* norms;
+};
 int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                      const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                      const int32_t* d_norms_pad,
                      int32_t* d_flags, int variant, int force, const struct KnnTuning& tn, int32_t* d_fix_list,
-                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
+                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches,
+                     const KnnQuery* query = nullptr);
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                       int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches);
 
@@ -95,6 +104,16 @@ int launch_mma_handshake_probe(int steps, int k_per_acc, int flags, int consumer
                                cudaStream_t st, int64_t* launches);
 
 // ---- filter.cu
+// Mutual check, sparse form: the train descriptors (and norms) of every surviving match, gathered to
+// q_desc / q_norms rows m_off[p] + i.
+void launch_mutual_gather(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off, const int64_t* d_row_off,
+                          const int64_t* d_m_off, const int32_t* d_mt, const uint8_t* d_desc, const int32_t* d_norms,
+                          uint8_t* d_q_desc, int32_t* d_q_norms, cudaStream_t st, int64_t* launches);
+// Keeps match i of pair p iff the nearest row of the QUERY image to its train descriptor
+// (d_knn_rev[m_off[p] + i].x) is its query row; compacts the lists in place and rewrites d_count.
+void launch_mutual_compact(int32_t n_pairs, const int64_t* d_row_off, const int64_t* d_m_off, const int4* d_knn_rev,
+                           int32_t* d_mq, int32_t* d_mt, int32_t* d_md2, int32_t* d_count, cudaStream_t st,
+                           int64_t* launches);
 void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img_off,
                    const int64_t* d_row_off, const int4* d_knn, const int64_t* d_row_off_rev,
                    const int4* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,

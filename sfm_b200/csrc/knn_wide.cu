@@ -285,8 +285,9 @@ __device__ __forceinline__ Top2K resolve_units(const Trk& s, int n_seen, const K
 // the CUDA cores by the WHOLE warp for one row at a time -- lane e and lane 16 + e each take 64
 // bytes of train row col + e (dp4a), the 16 keys are then fed to the row's lane in column order
 // and merged under the (key desc, index asc) order.  All lanes must call it (uniform control flow).
-__device__ __noinline__ Top2K recompute_units(Top2K r, bool need, int q_abs, int col, const uint8_t* __restrict__ desc,
-                                              int t_row, int t_cnt, const int32_t* __restrict__ nbase) {
+__device__ __noinline__ Top2K recompute_units(Top2K r, bool need, int q_abs, int col, const uint8_t* __restrict__ desc_q,
+                                              const uint8_t* __restrict__ desc, int t_row, int t_cnt,
+                                              const int32_t* __restrict__ nbase) {
     const int lane = threadIdx.x & 31;
     unsigned todo = __ballot_sync(0xffffffffu, need);
     while (todo) {
@@ -298,7 +299,7 @@ __device__ __noinline__ Top2K recompute_units(Top2K r, bool need, int q_abs, int
         const int part = lane >> 4;   // which 64-byte half of the 128-byte rows
         uint32_t dot = 0;
         if (c < t_cnt) {
-            const uint4* ap = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(qa) * kRowBytes) + 4 * part;
+            const uint4* ap = reinterpret_cast<const uint4*>(desc_q + static_cast<size_t>(qa) * kRowBytes) + 4 * part;
             const uint4* bp = reinterpret_cast<const uint4*>(desc + static_cast<size_t>(t_row + c) * kRowBytes) + 4 * part;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -358,9 +359,11 @@ struct SmemLayout {
 // MODE 0: the kNN.  1: max tree only, 2: no epilogue (timing probes; output is not a kNN).
 template <int MODE, bool SKIP>
 __global__ void __launch_bounds__(kThreads, 1)
-knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_x,
-                 const __grid_constant__ CUtensorMap tmap_ax, const uint8_t* __restrict__ desc,
-                 const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms, const int32_t* __restrict__ norms_pad,
+knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap,
+                 const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_ax,
+                 const uint8_t* __restrict__ desc_q, const int32_t* __restrict__ norms_q,
+                 const uint8_t* __restrict__ desc,
+                 const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms_pad,
                  int32_t* __restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns,
                  uint32_t epi_wait_ns, int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
@@ -377,6 +380,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     const int lane = threadIdx.x & 31;
 
     if (warp == kProducerWarp && lane == 0) {
+        tma_prefetch_desc(&tmap_q);
         tma_prefetch_desc(&tmap);
         tma_prefetch_desc(&tmap_x);
         tma_prefetch_desc(&tmap_ax);
@@ -421,7 +425,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 uint8_t* a_dst = sm.a + size_t(ap.stage) * kABlockBytes;
 #pragma unroll
                 for (int a = 0; a < kATiles; ++a)
-                    tma_load_2d(a_dst + a * kATileBytes, &tmap, &sm.a_full[ap.stage], 0, q_row + a * kTileM);
+                    tma_load_2d(a_dst + a * kATileBytes, &tmap_q, &sm.a_full[ap.stage], 0, q_row + a * kTileM);
             }
             __syncwarp();
             ap.advance();
@@ -505,7 +509,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             const long long out_row =
                 static_cast<long long>(static_cast<uint32_t>(w1.z)) | (static_cast<long long>(w1.w) << 32);
             const bool valid = row < q_cnt;
-            const int na = valid ? __ldg(norms + q_row + row) : 0;
+            const int na = valid ? __ldg(norms_q + q_row + row) : 0;
             const int n_tiles = (t_cnt + kTileN - 1) / kTileN;
             const int32_t* nbase = norms_pad + t_pad;
             KeyFmt kf;
@@ -589,7 +593,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             // the best dropped one is recomputed here, a second one sends the row to knn_fix_kernel
             const uint32_t mf = kf.ubits + 1;
             r = recompute_units(r, valid && n_in >= 3 && (sk.dm >> mf) == (sk.k2 >> mf), q_row + row,
-                                key_col(sk.dm, kf, colbase), desc, t_row, t_cnt, nbase);
+                                key_col(sk.dm, kf, colbase), desc_q, desc, t_row, t_cnt, nbase);
             const bool tie = n_in >= 4 && (sk.dd >> mf) == (sk.k2 >> mf);
             // the thread of the upper column half hands its top-2 to the lower half's thread,
             // which merges under the (key, lowest index) order and writes the row
@@ -687,7 +691,8 @@ __global__ void bias32_kernel(const int32_t* __restrict__ norms, long long total
 // time: threads stride over the train columns (ascending per thread, strict compares), partial
 // top-2s merged under the (key desc, index asc) order = OpenCV's lowest-index tie rule.  Rows
 // beyond the list capacity (degenerate data: everything ties) are found by scanning the work items.
-__device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, const uint8_t* __restrict__ desc,
+__device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, const uint8_t* __restrict__ desc_q,
+                        const int32_t* __restrict__ norms_q, const uint8_t* __restrict__ desc,
                         const int32_t* __restrict__ norms, int4* __restrict__ out, Top2K* s_part) {
     const int4 w0 = __ldg(reinterpret_cast<const int4*>(work + w));
     const int4 w1 = __ldg(reinterpret_cast<const int4*>(work + w) + 1);
@@ -698,7 +703,7 @@ __device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, c
     uint4 a[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-        a[i] = __ldg(reinterpret_cast<const uint4*>(desc + static_cast<size_t>(q_row + r) * kRowBytes) + i);
+        a[i] = __ldg(reinterpret_cast<const uint4*>(desc_q + static_cast<size_t>(q_row + r) * kRowBytes) + i);
     Top2K best{INT_MIN, INT_MIN, INT_MAX, INT_MAX};
 #pragma unroll 2
     for (int c = threadIdx.x; c < t_cnt; c += SFM_QBLOCK) {
@@ -745,7 +750,7 @@ __device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, c
     if (threadIdx.x == 0) {
         Top2K m = s_part[0];
         for (int k = 1; k < SFM_QBLOCK / 32; ++k) m = merge(m, s_part[k]);
-        const int na = __ldg(norms + q_row + r);
+        const int na = __ldg(norms_q + q_row + r);
         const int i1 = m.i1 == INT_MAX ? -1 : m.i1;
         const int i2 = m.i2 == INT_MAX ? -1 : m.i2;
         out[out_row + r] = make_int4(i1, i2, i1 < 0 ? INT_MAX : na - m.k1, i2 < 0 ? INT_MAX : na - m.k2);
@@ -754,6 +759,8 @@ __device__ void fix_row(const WorkItem* __restrict__ work, long long w, int r, c
 }
 
 __global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __restrict__ work, long long n_work,
+                                                             const uint8_t* __restrict__ desc_q,
+                                                             const int32_t* __restrict__ norms_q,
                                                              const uint8_t* __restrict__ desc,
                                                              const int32_t* __restrict__ norms,
                                                              const int32_t* __restrict__ flags,
@@ -767,7 +774,7 @@ __global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __r
     const int n_list = cnt < fix_cap ? cnt : fix_cap;
     for (int e = blockIdx.x; e < n_list; e += gridDim.x) {
         const int2 it = __ldg(fix_list + e);
-        fix_row(work, it.x, it.y, desc, norms, out, s_part);
+        fix_row(work, it.x, it.y, desc_q, norms_q, desc, norms, out, s_part);
     }
     if (cnt <= fix_cap) return;
     for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {   // list overflow: scan for the markers
@@ -781,7 +788,7 @@ __global__ void __launch_bounds__(SFM_QBLOCK) knn_fix_kernel(const WorkItem* __r
             s_list[atomicAdd(&s_n, 1)] = threadIdx.x;
         __syncthreads();
         const int n = s_n;
-        for (int k = 0; k < n; ++k) fix_row(work, w, s_list[k], desc, norms, out, s_part);
+        for (int k = 0; k < n; ++k) fix_row(work, w, s_list[k], desc_q, norms_q, desc, norms, out, s_part);
         __syncthreads();
     }
 }
@@ -850,8 +857,8 @@ debug_wide_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
 }
 
 template <int MODE, bool SKIP>
-cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
-                           const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
+cudaError_t launch_variant(const KnnQuery& q, const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
+                           const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work,
                            const int32_t* d_norms_pad, int32_t* d_flags, int force, const KnnTuning& tn,
                            int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid, cudaStream_t st) {
     static bool configured = false;
@@ -861,7 +868,8 @@ cudaError_t launch_variant(const CUtensorMap& tmap, const CUtensorMap& tmap_x, c
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    knn2_wide_kernel<MODE, SKIP><<<grid, kThreads, kSmemBytes, st>>>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms,
+    knn2_wide_kernel<MODE, SKIP><<<grid, kThreads, kSmemBytes, st>>>(*q.tmap, tmap, tmap_x, tmap_ax, q.desc, q.norms, d_desc,
+                                                              d_work, n_work,
                                                               d_norms_pad, d_flags, force, tn.probe_flags, tn.wait_ns,
                                                               tn.epi_wait_ns, d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
@@ -882,28 +890,31 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
                      const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
                      const int32_t* d_norms_pad,
                      int32_t* d_flags, int variant, int force, const KnnTuning& tn, int32_t* d_fix_list,
-                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches) {
+                     int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches,
+                     const KnnQuery* query) {
     if (n_work <= 0) return 0;
+    // query rows: the registered descriptor array itself unless the caller brings its own (mutual check)
+    const KnnQuery q = query ? *query : KnnQuery{&tmap, d_desc, d_norms};
     const unsigned grid = static_cast<unsigned>(n_work < num_sms ? n_work : num_sms);
     int2* fl = reinterpret_cast<int2*>(d_fix_list);
     cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, sizeof(int32_t), st);   // length of this launch's fix list
     if (e != cudaSuccess) return static_cast<int>(e);
     if (variant == 1)
-        e = launch_variant<1, false>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1,
+        e = launch_variant<1, false>(q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags, 1,
                                      tn, fl, fix_cap, d_knn, grid, st);
     else if (variant == 2)
-        e = launch_variant<2, false>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags, 1,
+        e = launch_variant<2, false>(q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags, 1,
                                      tn, fl, fix_cap, d_knn, grid, st);
     else if (variant == 3)   // the kNN WITH the warp-uniform skip of the unit bookkeeping (A/B: 5 % slower)
-        e = launch_variant<0, true>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags,
+        e = launch_variant<0, true>(q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags,
                                     force, tn, fl, fix_cap, d_knn, grid, st);
     else
-        e = launch_variant<0, false>(tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms, d_norms_pad, d_flags,
+        e = launch_variant<0, false>(q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags,
                                      force, tn, fl, fix_cap, d_knn, grid, st);
     ++*launches;
     if (e == cudaSuccess && (variant == 0 || variant == 3) && !(tn.probe_flags & 4u)) {   // (probe bit 2: main kernel alone)
-        knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_flags, fl, fix_cap,
-                                                          reinterpret_cast<int4*>(d_knn));
+        knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, q.desc, q.norms, d_desc, d_norms, d_flags, fl,
+                                                          fix_cap, reinterpret_cast<int4*>(d_knn));
         ++*launches;
         e = cudaGetLastError();
     }
@@ -913,7 +924,7 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
 int launch_knn_fix(const WorkItem* d_work, int64_t n_work, const uint8_t* d_desc, const int32_t* d_norms,
                    const int32_t* d_flags, const int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms,
                    cudaStream_t st, int64_t* launches) {
-    knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_flags,
+    knn_fix_kernel<<<2 * num_sms, SFM_QBLOCK, 0, st>>>(d_work, n_work, d_desc, d_norms, d_desc, d_norms, d_flags,
                                                       reinterpret_cast<const int2*>(d_fix_list), fix_cap,
                                                       reinterpret_cast<int4*>(d_knn));
     ++*launches;

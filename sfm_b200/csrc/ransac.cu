@@ -167,9 +167,15 @@ __device__ bool warp_refit_from_normal(const double (&ata)[45], double c1x, doub
     return ok;
 }
 
-__device__ void write_skip(int p, int m, int status, double* F_out, sfm_pair_metrics* metrics,
-                           int32_t* status_out) {
+// A skipped pair leaves defined outputs behind (F = 0, no inlier, errors 0): what a caller packs with
+// only_ok = 0 is then a pure function of the pair, whichever rank or chunk computed it.
+__device__ void write_skip(int p, int m, int status, long long base, uint8_t* mask, float* sym, double* F_out,
+                           sfm_pair_metrics* metrics, int32_t* status_out) {
     if (threadIdx.x < 9 && F_out) F_out[9ll * p + threadIdx.x] = 0.0;
+    for (int i = threadIdx.x; i < m; i += kThreads) {
+        mask[base + i] = 0;
+        sym[base + i] = 0.f;
+    }
     if (threadIdx.x == 0) {
         sfm_pair_metrics mt;
         mt.total_matches = m;
@@ -211,11 +217,11 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
             __syncthreads();
         } else {
             if (m < prm.min_matches) {
-                write_skip(p, m, SFM_PAIR_TOO_FEW_MATCHES, F_out, metrics, status_out);
+                write_skip(p, m, SFM_PAIR_TOO_FEW_MATCHES, base, mask, sym, F_out, metrics, status_out);
                 continue;
             }
             if (m < kMinSample) {
-                write_skip(p, m, SFM_PAIR_NO_MODEL, F_out, metrics, status_out);
+                write_skip(p, m, SFM_PAIR_NO_MODEL, base, mask, sym, F_out, metrics, status_out);
                 continue;
             }
             const uint64_t key = pair_ids ? rc::pair_key(prm.seed, pair_ids[2 * p], pair_ids[2 * p + 1])
@@ -327,7 +333,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
             }
             ransac_it = done < limit ? done : limit;
             if (sh.best_cnt < kMinSample) {
-                write_skip(p, m, SFM_PAIR_NO_MODEL, F_out, metrics, status_out);
+                write_skip(p, m, SFM_PAIR_NO_MODEL, base, mask, sym, F_out, metrics, status_out);
                 continue;
             }
             ransac_inl = sh.best_cnt;

@@ -59,7 +59,10 @@ class PairEngine:
         self.ctx = L.Context(device)
         self.device = self.ctx.device
         self.ratio = float(ratio)
+        # mutual: False, True / "sparse" (only the surviving matches' train descriptors are matched back:
+        # sfm_mutual_filter) or "full" (a second exhaustive kNN pass over the reversed pairs)
         self.mutual = bool(mutual)
+        self.mutual_full = mutual == "full"
         self.params = params if params is not None else L.default_params()
         self.max_rows = int(max_rows_per_chunk)
         self.counts = None
@@ -73,6 +76,7 @@ class PairEngine:
         self.ctx.set_images(desc, kps, offsets)
         self.counts = self.ctx.counts
         self.n_images = len(self.counts)
+        self._sparse_ok = None      # fold-range flag of this set, read when the mutual check first needs it
 
     def upload_images(self, desc_host, kps_host, offsets):
         """Host (ideally pinned) tensors -> device, then register.  Returns bytes copied."""
@@ -94,7 +98,7 @@ class PairEngine:
     # --------------------------------------------------------------- chunks
     def _chunks(self, pairs):
         rows = self.counts[pairs[:, 0]].astype(np.int64)
-        if self.mutual:
+        if self.mutual and self._full_reverse():
             rows = np.maximum(rows, self.counts[pairs[:, 1]].astype(np.int64))
         lo, acc = 0, 0
         for p in range(len(pairs)):
@@ -104,6 +108,13 @@ class PairEngine:
             acc += rows[p]
         if lo < len(pairs):
             yield lo, len(pairs)
+
+    def _full_reverse(self) -> bool:
+        if self.mutual_full:
+            return True
+        if self._sparse_ok is None:
+            self._sparse_ok = int(self.counts.sum()) == 0 or not self.ctx.fold_flag()
+        return not self._sparse_ok
 
     # ----------------------------------------------------------- device path
     def match_device(self, pairs, only_ok: bool = True):
@@ -149,7 +160,8 @@ class PairEngine:
         self._mark("begin")
         ctx.knn2(pairs, ro, knn)
         knn_rev = ro_rev = None
-        if self.mutual:
+        sparse = self.mutual and not self._full_reverse()
+        if self.mutual and not sparse:
             rev = np.ascontiguousarray(pairs[:, ::-1])
             ro_rev = ctx.query_rows(rev)
             knn_rev = self._buf("knn_rev", (int(ro_rev[-1]), 4), torch.int32)
@@ -158,6 +170,14 @@ class PairEngine:
         out = (self._buf("mq", (n,), torch.int32), self._buf("mt", (n,), torch.int32),
                self._buf("md2", (n,), torch.int32), self._buf("count", (P,), torch.int32))
         mq, mt, md2, cnt = ctx.filter_matches(pairs, ro, knn, self.ratio, ro_rev, knn_rev, out=out)
+        if sparse:
+            # the one host round trip of the sparse mutual check: the per-pair survivor counts size the
+            # reverse pass (a few hundred descriptors per pair instead of the whole train image)
+            if getattr(self, "_cnt_pin", None) is None or self._cnt_pin.numel() < P:
+                self._cnt_pin = torch.empty(max(P, 1024), dtype=torch.int32, pin_memory=True)
+            self._cnt_pin[:P].copy_(cnt, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            ctx.mutual_filter(pairs, ro, self._cnt_pin[:P].numpy(), mq, mt, md2, cnt)
         self._mark("filter")
         v = ctx.verify_pairs(pairs, ro, mq, mt, cnt, self.params)
         self._mark("ransac")

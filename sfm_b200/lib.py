@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_knn_profile", "sfm_debug_knn_profile_events", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_mutual_filter", "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_knn_profile", "sfm_debug_knn_profile_events", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -78,6 +78,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_set_images.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.sfm_knn2.argtypes = [vp, vp, i32, vp, vp, vp]
     lib.sfm_filter_matches.argtypes = [vp, vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp, vp, vp]
+    lib.sfm_mutual_filter.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.sfm_verify_pairs.argtypes = [vp, vp, i32, vp, vp, vp, vp, C.POINTER(VerifyParams),
                                      vp, vp, vp, vp, vp, vp, vp, vp]
     lib.sfm_verify_given_F.argtypes = [vp, i32, vp, vp, vp, vp, C.POINTER(VerifyParams),
@@ -231,6 +232,24 @@ class Context:
         self._check(self.lib.sfm_knn2(self.h, _h(pairs), len(pairs), _h(row_off),
                                       self._dev(out, torch.int32), self._stream()))
         return out, row_off
+
+    # -- K2, mutual check in its sparse form
+    def mutual_filter(self, pairs, row_off, count_host, mq, mt, md2, count):
+        """Keep only the matches whose query row is the nearest row of the query image to their train
+        descriptor; lists compacted in place, `count` rewritten.  count_host: int32 host copy of `count`."""
+        torch = self.torch
+        pairs = _pairs(pairs)
+        row_off = _i64(row_off)
+        ch = np.ascontiguousarray(np.asarray(count_host, np.int32))
+        self._check(self.lib.sfm_mutual_filter(
+            self.h, _h(pairs), len(pairs), _h(row_off), _h(ch), self._dev(mq, torch.int32),
+            self._dev(mt, torch.int32), self._dev(md2, torch.int32), self._dev(count, torch.int32), self._stream()))
+
+    def fold_flag(self) -> bool:
+        """True when a registered descriptor's norm is beyond the folded kNN kernels' range (one sync)."""
+        f = C.c_int32(0)
+        self._check(self.lib.sfm_debug_fold_flag(self.h, C.byref(f), self._stream()))
+        return f.value != 0
 
     # -- K2
     def filter_matches(self, pairs, row_off, knn, ratio=0.75, row_off_rev=None, knn_rev=None, out=None):

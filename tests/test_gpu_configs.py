@@ -31,11 +31,14 @@ def _bunny(golden_dir):
     return z, off, descs, kps
 
 
-def test_mutual_engine_bunny_all_pairs(golden_dir):
+@pytest.mark.parametrize("mutual", [True, "full"])
+def test_mutual_engine_bunny_all_pairs(golden_dir, mutual):
+    """mutual=True: the sparse form (sfm_mutual_filter: only the surviving matches' train descriptors go
+    back against the query image); "full": a second exhaustive kNN pass over the reversed pairs."""
     from sfm_b200 import lib as L, synth
     from sfm_b200.engine import PairEngine
     z, off, descs, kps = _bunny(golden_dir)
-    eng = PairEngine(0, mutual=True)
+    eng = PairEngine(0, mutual=mutual)
     eng.upload_images(torch.from_numpy(z["desc"]), torch.from_numpy(z["kps"].astype(np.float32)), off.astype(np.int64))
     pairs = synth.all_pairs(len(descs)).numpy()
     res = eng.match_pairs(pairs, only_ok=False)
@@ -83,11 +86,12 @@ def test_mutual_image_matcher_writes_mutual_lists(tmp_path, golden_dir):
     assert [g.queryIdx for g in got] == q.tolist() and [g.trainIdx for g in got] == t.tolist()
 
 
-def test_mutual_8k_pair():
+@pytest.mark.parametrize("mutual", [True, "full"])
+def test_mutual_8k_pair(mutual):
     from sfm_b200 import synth
     from sfm_b200.engine import PairEngine
     s = synth.make_image_set(3, 8192, seed=synth.BASE_SEED + 9, tie_frac=0.01)
-    eng = PairEngine(0, mutual=True)
+    eng = PairEngine(0, mutual=mutual)
     eng.upload_images(s.desc, s.kps, s.offsets.numpy())
     pairs = np.array([(0, 1), (2, 1)], np.int32)
     res = eng.match_pairs(pairs, only_ok=False)
@@ -97,6 +101,25 @@ def test_mutual_8k_pair():
         sl = res.pair_slice(p)
         assert len(q) > 100
         assert np.array_equal(res.query_idx[sl], q) and np.array_equal(res.train_idx[sl], t)
+        assert np.array_equal(res.distance(p), d)
+
+
+def test_mutual_sparse_many_chunks_and_duplicates():
+    """The sparse mutual check over several chunks, on a set with 5 % duplicated rows (the reverse side's
+    lowest-index rule decides) and images of very different sizes."""
+    from sfm_b200 import synth
+    from sfm_b200.engine import PairEngine
+    sizes = [900, 400, 1300, 700, 257, 1000]
+    s = synth.make_image_set(len(sizes), sizes, seed=23, shared_frac=0.6, tie_frac=0.05)
+    pairs = np.array([(i, j) for i in range(len(sizes)) for j in range(len(sizes)) if i != j], np.int32)
+    eng = PairEngine(0, mutual=True, max_rows_per_chunk=2500)
+    eng.upload_images(s.desc, s.kps, s.offsets.numpy())
+    assert sum(1 for _ in eng._chunks(pairs)) > 4
+    res = eng.match_pairs(pairs, only_ok=False)
+    for p, (i, j) in enumerate(pairs):
+        q, t, d = oknn.match_features(s.image(int(i))[0].numpy(), s.image(int(j))[0].numpy(), mutual=True)
+        sl = res.pair_slice(p)
+        assert np.array_equal(res.query_idx[sl], q) and np.array_equal(res.train_idx[sl], t), (i, j)
         assert np.array_equal(res.distance(p), d)
 
 
