@@ -331,10 +331,13 @@ def run_b200(args):
         launches0 = eng.ctx.launches
         barrier()
         clk.mark()
+        host_ms = []
         for e0, e1 in ev:
             flush.zero_()
             e0.record()
+            t_h = time.perf_counter()
             chunks = eng.match_device(my_pairs)
+            host_ms.append((time.perf_counter() - t_h) * 1e3)
             e1.record()
         barrier()
         launches = eng.ctx.launches - launches0
@@ -342,8 +345,8 @@ def run_b200(args):
         ms_total = max_over_ranks(sum(my_steps))
         ms_step = ms_total / args.steps
         # per-rank view of the same steps (mean, slowest step): a straggling rank or a host-side gap shows here
-        by_rank = [(round(float(np.mean(x)), 3), round(float(np.max(x)), 3))
-                   for x in (D.all_gather_objects(my_steps) if world > 1 else [my_steps])]
+        by_rank = [(round(float(np.mean(x)), 3), round(float(np.max(x)), 3), round(float(np.mean(h)), 3))
+                   for x, h in (D.all_gather_objects((my_steps, host_ms)) if world > 1 else [(my_steps, host_ms)])]
         n_ok = sum(int((c["status"] == L.PAIR_OK).sum().item()) for c in chunks)
         n_matches = sum(int(c["count"].sum().item()) for c in chunks)
         hyp_pts = 0.0
@@ -555,7 +558,8 @@ def run_b200(args):
             "run": {"pairs_passing_verification": n_ok, "matches_after_ratio": n_matches,
                     "parallelism": f"pair list cut into {world} contiguous ranges of equal n_i*n_j",
                     "l2": "flushed between steps (256 MiB write)",
-            "ms_per_step_by_rank_mean_max": by_rank,
+            "ms_per_step_by_rank_mean_max_hostenqueue": by_rank,
+            "rank0_step_ms": [round(x, 2) for x in my_steps], "rank0_host_enqueue_ms": [round(x, 2) for x in host_ms],
                     "ransac_hypotheses_x_points_per_sec_rank0": hyp_pts / (ransac_ms * 1e-3) if ransac_ms > 0 else None},
             "comparisons_per_sec": cmp_s, "int8_tops": whole_tops,
             "whole_step_frac_of_nominal_int8": whole_tops / (NOMINAL_INT8_TOPS * world),

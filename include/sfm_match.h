@@ -241,11 +241,6 @@ SFM_API int sfm_probe_int8_rate(sfm_ctx* ctx, int32_t iters, int32_t tile_n, flo
  * written to d_out i32 [128,128]. */
 SFM_API int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream);
 
-/* Debug: the same tile with the fold step (see sfm_b200/csrc/knn.cu): accumulators
- * a.b + 2016029 - floor(||b||^2 / 2) for query rows q_row.. against tile `tile` (128 rows) of
- * `train_image`, written to d_out i32 [128,128]. */
-SFM_API int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_t tile,
-                        int32_t* d_out, void* stream);
 /* Debug: folded accumulators of one 128 x 256 tile through the wide kernel's path
  * (sfm_b200/csrc/knn_wide.cu: N = 256 MMAs, fold operand as SWIZZLE_32B rows):
  * a.b + 2016029 - floor(||b||^2 / 2) for query rows q_row.. against descriptor rows t_row..,
@@ -280,31 +275,26 @@ SFM_API int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k
                                   int32_t consumers, float* ms, void* stream);
 /* Select the kNN kernel variant used by sfm_knn2: 0 automatic (wide folded kernel, N = 256
  * MMAs with the norm term folded into the contraction, unless a registered row has
- * ||b||^2 > 4,032,059, then the generic variant), 1 generic only, 2 N = 128 folded kernel only,
- * 5 wide folded kernel only; timing probes whose output is NOT a kNN: 3 / 6 max tree only
- * (N = 128 / wide), 4 / 7 TMA + MMA pipeline without an epilogue. */
+ * ||b||^2 > 4,032,059, then the generic variant), 1 generic only, 5 wide folded kernel only,
+ * 12 CTA-pair folded kernel (knn_pair.cu: cta_group::2, four accumulator stages), 15 wide kernel
+ * with the warp-uniform skip of the unit bookkeeping (measured slower; kept for the A/B);
+ * timing probes whose output is NOT a kNN: 6 / 13 max tree only (wide / pair), 7 / 14 TMA + MMA
+ * pipeline without an epilogue. */
 SFM_API int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode);
 /* mbarrier suspend-time hints (ns; 0 = spin) of the kNN kernel's producer/MMA warps and of
  * its epilogue warps.  Tuning knob; results do not depend on it. */
 SFM_API int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_wait_ns);
 /* Probe switches of the kNN kernel.  Timing probes (results become meaningless): bit 0 the
- * producer skips the train-tile TMA loads (N = 128 kernel), bit 1 the MMA warp skips the tcgen05.mma
+ * producer skips the train-tile TMA loads (generic and pair kernels), bit 1 the MMA warp skips the tcgen05.mma
  * issue, bit 2 the wide kernel runs without its fix-up pass.  Test switch (results stay exact):
  * bit 3 shrinks the wide kernel's fix-up list to 4 entries, so its overflow scan is exercised. */
 SFM_API int sfm_debug_set_knn_probe_flags(sfm_ctx* ctx, int32_t flags);
-/* Profiling build of the TS kNN kernel: enable != 0 makes the following sfm_knn2 calls run the
- * instrumented variant (clock64 counters around every barrier wait).  h_sum16 (may be NULL) receives
- * the counters of the last instrumented launch summed over the CTAs (layout: knn_ts.cu); synchronises. */
-SFM_API int sfm_debug_knn_profile(sfm_ctx* ctx, int32_t enable, int64_t* h_sum16, void* stream);
 /* Hand-over latency probe (one CTA): n_mma tcgen05.mma (128 x tile_n x 32, tile_n = 128 or 256) + commit by
  * one warp, a second warp waits and answers through a plain mbarrier.  h_out4 = mean cycles of: issue,
  * issue start -> other warp woken, its arrive -> issuer woken, issue start -> issuer itself woken.
  * trail > 0: that many more MMAs (another accumulator) are issued right after the commit. */
 SFM_API int sfm_debug_handover_probe(sfm_ctx* ctx, int32_t iters, int32_t n_mma, int32_t tile_n, int32_t trail,
                              int64_t* h_out4, void* stream);
-/* Time stamps of CTA 0's first 4096 accumulator groups in the last instrumented launch:
- * h_events i64 [5][4096] (kinds: knn_ts.cu).  Synchronises. */
-SFM_API int sfm_debug_knn_profile_events(sfm_ctx* ctx, int64_t* h_events, void* stream);
 /* Reads (synchronising `stream`) whether the registered set exceeded the fold range. */
 SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);
 

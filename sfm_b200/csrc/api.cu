@@ -99,20 +99,17 @@ struct sfm_ctx {
     int32_t n_images = 0;
     int64_t total_rows = 0;
     int64_t pad_total = 0;
-    std::vector<int64_t> h_off, h_pad, h_x;
-    CUtensorMap tmap, tmap_x;
+    std::vector<int64_t> h_off, h_pad;
+    CUtensorMap tmap;
     CUtensorMap tmap_x32, tmap_ax32;   // wide kNN variant: fold operands as 32-byte rows (knn_wide.cu)
     CUtensorMap tmap_b64, tmap_x64;    // pair kNN variant: 64-row boxes of the descriptor / fold operand rows (knn_pair.cu)
     DevBuf<uint8_t> d_bias32;
     DevBuf<int32_t> d_fix_list;  // (work item, row) of the rows the wide kNN kernel leaves to its fix-up pass
     static constexpr int32_t kFixCap = 1 << 18;
     bool have_tmap = false;
-    DevBuf<int64_t> d_img_off, d_pad_off, d_x_off;
+    DevBuf<int64_t> d_img_off, d_pad_off;
     DevBuf<int32_t> d_norms, d_norms_pad, d_flags;
-    DevBuf<long long> d_prof;      // cycle counters of the TS kernel's profiling build (sfm_debug_knn_profile)
-    bool knn_prof = false;
     DevBuf<uint32_t> d_par_bits;   // norm parities of the padded column space, 32 per word (knn_ts.cu)
-    DevBuf<uint8_t> d_bias;      // fold-step operands (see knn.cu)
     // sfm_mutual_filter scratch: gathered train descriptors / norms of the surviving matches, their
     // reverse kNN rows, the per-pair match offsets and the reverse pass's work items
     DevBuf<uint8_t> d_qdesc;
@@ -123,7 +120,7 @@ struct sfm_ctx {
     std::vector<sfm::WorkItem> h_work_rev;
     int fold_flag_host = -1;     // flags[0] read back once per image set (-1: not yet)
     int knn_mode = 0;            // sfm_debug_set_knn_mode
-    int knn_auto = 5;            // what mode 0 resolves to: 5 = wide fold kernel + generic, 8 = TS kernel + generic
+    int knn_auto = 5;            // what mode 0 resolves to: 5 = wide folded kernel + generic fallback
     sfm::KnnTuning knn_tuning;   // sfm_debug_set_knn_waits
 
     // per-call metadata scratch
@@ -271,9 +268,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_pad_off.release();
     ctx->d_norms.release();
     ctx->d_norms_pad.release();
-    ctx->d_x_off.release();
     ctx->d_flags.release();
-    ctx->d_bias.release();
     ctx->d_bias32.release();
     ctx->d_qdesc.release();
     ctx->d_qnorms.release();
@@ -281,7 +276,6 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_moff.release();
     ctx->d_work_rev.release();
     ctx->d_par_bits.release();
-    ctx->d_prof.release();
     ctx->d_fix_list.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
@@ -324,28 +318,14 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
     }
     ctx->pad_total = ctx->h_pad[n_images];
     if (ctx->pad_total >= (int64_t(1) << 31)) return ctx->fail("padded column space too large");
-    // fold-step bias rows: 128 constant rows, then 128 rows per 512 train rows of each image
-    ctx->h_x.resize(n_images + 1);
-    ctx->h_x[0] = SFM_TTILE;
-    for (int i = 0; i < n_images; ++i) {
-        const int64_t n = h_offsets[i + 1] - h_offsets[i];
-        ctx->h_x[i + 1] = ctx->h_x[i] + (n + 4 * SFM_TTILE - 1) / (4 * SFM_TTILE) * SFM_TTILE;
-    }
-    const int64_t x_rows = ctx->h_x[n_images];
-    if (x_rows >= (int64_t(1) << 31)) return ctx->fail("bias row space too large");
-
     SFM_CUDA(ctx, ctx->d_img_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_pad_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_norms.reserve(static_cast<size_t>(total) + 1));
     SFM_CUDA(ctx, ctx->d_norms_pad.reserve(static_cast<size_t>(ctx->pad_total) + 4));
-    SFM_CUDA(ctx, ctx->d_x_off.reserve(n_images + 1));
     SFM_CUDA(ctx, ctx->d_flags.reserve(4));
-    SFM_CUDA(ctx, ctx->d_bias.reserve(static_cast<size_t>(x_rows) * SFM_DESC_DIM));
     SFM_CUDA(ctx, ctx->d_bias32.reserve(static_cast<size_t>(total + SFM_TTILE) * 32));
     SFM_CUDA(ctx, ctx->d_fix_list.reserve(2 * static_cast<size_t>(sfm_ctx::kFixCap)));
     SFM_CUDA(ctx, ctx->d_par_bits.reserve(static_cast<size_t>(ctx->pad_total) / 32 + 4));
-    SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_x_off.p, ctx->h_x.data(), sizeof(int64_t) * (n_images + 1),
-                                  cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_img_off.p, ctx->h_off.data(), sizeof(int64_t) * (n_images + 1),
                                   cudaMemcpyHostToDevice, st));
     SFM_CUDA(ctx, cudaMemcpyAsync(ctx->d_pad_off.p, ctx->h_pad.data(), sizeof(int64_t) * (n_images + 1),
@@ -362,11 +342,6 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled failed: CUresult %d", int(r));
-        const cuuint64_t xdim[2] = {SFM_DESC_DIM, static_cast<cuuint64_t>(x_rows)};
-        r = ctx->encode(&ctx->tmap_x, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ctx->d_bias.p, xdim, gstride, box,
-                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (bias) failed: CUresult %d", int(r));
         // wide variant: u8 [128 + total, 32], 256-row boxes (train tile) and a 128-row box (constant rows)
         const cuuint64_t wdim[2] = {32, static_cast<cuuint64_t>(total + SFM_TTILE)};
         const cuuint64_t wstride[1] = {32};
@@ -392,8 +367,8 @@ int sfm_set_images(sfm_ctx* ctx, const uint8_t* d_desc, const float* d_kps,
         if (r != CUDA_SUCCESS) return ctx->fail("cuTensorMapEncodeTiled (64-row boxes) failed: CUresult %d", int(r));
         ctx->have_tmap = true;
     }
-    sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, ctx->d_x_off.p, n_images,
-                      ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_bias.p, ctx->d_flags.p, st, &ctx->launches);
+    sfm::launch_norms(d_desc, total, ctx->d_img_off.p, ctx->d_pad_off.p, n_images, ctx->d_norms.p,
+                      ctx->d_norms_pad.p, ctx->d_flags.p, st, &ctx->launches);
     sfm::launch_bias32(ctx->d_norms.p, total, ctx->d_bias32.p, ctx->d_flags.p, st, &ctx->launches);
     sfm::launch_parity_bits(ctx->d_norms_pad.p, ctx->pad_total, ctx->d_par_bits.p, st, &ctx->launches);
     SFM_CUDA(ctx, cudaGetLastError());
@@ -431,18 +406,14 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
         return 1;
     SFM_CUDA(ctx, ctx->d_work.reserve(static_cast<size_t>(n_work) + 1));
     sfm::launch_build_work(ctx->d_pairs.p, n_pairs, d_prefix, d_row, ctx->d_img_off.p, ctx->d_pad_off.p,
-                           ctx->d_x_off.p, ctx->d_work.p, st, &ctx->launches);
-    // knn_mode 0: the TS kernel (knn_ts.cu), or the generic one when a norm is beyond the fold range (both are
-    // launched; the one that does not apply exits at its first instruction).  1: generic, 2-4: N = 128
-    // folded kernel and its probes (knn.cu), 5: wide kernel only (knn_wide.cu), 6/7: its timing probes,
-    // 8: TS kernel only, 10/11: its timing probes.
+                           ctx->d_work.p, st, &ctx->launches);
+    // knn_mode 0: the wide folded kernel (knn_wide.cu), or the generic one when a norm is beyond the fold range
+    // (both are launched; the one that does not apply exits at its first instruction).  1: generic only,
+    // 5: wide only, 6/7: its timing probes, 12: CTA-pair kernel (knn_pair.cu), 13/14: its timing probes,
+    // 15: wide with the warp-uniform skip of the unit bookkeeping.
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
-    if (km >= 8 && km < 12 && ctx->knn_prof) {
-        SFM_CUDA(ctx, ctx->d_prof.reserve(static_cast<size_t>(ctx->num_sms) * 16 + 5 * 4096));
-        SFM_CUDA(ctx, cudaMemsetAsync(ctx->d_prof.p, 0, sizeof(long long) * (ctx->num_sms * 16 + 5 * 4096), st));
-    }
     if (km == 15)   // wide kernel with the warp-uniform skip of the unit bookkeeping (A/B against mode 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, 3, 1, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap,
@@ -452,22 +423,15 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
                                   n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
                                   km - 12, ctx->knn_mode != 0, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
                                   ctx->num_sms, st, &ctx->launches);
-    else if (km >= 8)
-        r = sfm::launch_knn2_ts(ctx->tmap, ctx->tmap_ax32, ctx->d_desc, ctx->d_bias32.p, ctx->d_work.p, n_work,
-                                ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
-                                km == 10 ? 1 : (km == 11 ? 2 : 0), ctx->knn_mode != 0, ctx->knn_tuning,
-                                ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches,
-                                ctx->knn_prof ? ctx->d_prof.p : nullptr);
     else if (km >= 5)
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
                                   ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
                                   ctx->num_sms, st, &ctx->launches);
-    const bool folded_auto = (km == 5 || km == 8 || km == 12) && ctx->knn_mode == 0;
-    if (!r && (km < 5 || folded_auto))
-        r = sfm::launch_knn2(ctx->tmap, ctx->tmap_x, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
-                             ctx->d_norms_pad.p, ctx->d_flags.p, folded_auto ? 9 : km, ctx->knn_tuning, d_knn,
-                             ctx->num_sms, st, &ctx->launches);
+    const bool folded_auto = (km == 5 || km == 12) && ctx->knn_mode == 0;
+    if (!r && (km == 1 || folded_auto))
+        r = sfm::launch_knn2(ctx->tmap, ctx->d_work.p, n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_flags.p,
+                             folded_auto ? 1 : 0, ctx->knn_tuning, d_knn, ctx->num_sms, st, &ctx->launches);
     if (r) return ctx->fail("knn2 launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     return 0;
 }
@@ -524,7 +488,7 @@ int sfm_mutual_filter(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, con
             w.t_row = static_cast<int32_t>(ctx->h_off[qi]);
             w.t_cnt = static_cast<int32_t>(nq);
             w.t_pad = static_cast<int32_t>(ctx->h_pad[qi]);
-            w.x_row = static_cast<int32_t>(ctx->h_x[qi]);
+            w.x_row = 0;
             w.out_row = ctx->h_moff[p] + b;
             ctx->h_work_rev.push_back(w);
         }
@@ -796,26 +760,7 @@ int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_ou
     if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
     if (!d_out) return ctx->fail("d_out is NULL");
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));
-    int r = sfm::launch_debug_dot(ctx->tmap, ctx->tmap_x, static_cast<int32_t>(q_row),
-                                  static_cast<int32_t>(t_row), -1, 0, d_out,
-                                  static_cast<cudaStream_t>(stream), &ctx->launches);
-    if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
-    return 0;
-}
-
-int sfm_debug_fold_tile(sfm_ctx* ctx, int64_t q_row, int32_t train_image, int32_t tile, int32_t* d_out,
-                        void* stream) {
-    if (!ctx) return 1;
-    if (!ctx->have_tmap) return ctx->fail("no descriptors registered");
-    if (!d_out) return ctx->fail("d_out is NULL");
-    if (train_image < 0 || train_image >= ctx->n_images) return ctx->fail("train image out of range");
-    const int64_t n = ctx->h_off[train_image + 1] - ctx->h_off[train_image];
-    if (tile < 0 || int64_t(tile) * SFM_TTILE >= n) return ctx->fail("tile out of range");
-    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
-    const int64_t t_row = ctx->h_off[train_image] + int64_t(tile) * SFM_TTILE;
-    const int64_t x_row = ctx->h_x[train_image] + int64_t(tile / 4) * SFM_TTILE;
-    int r = sfm::launch_debug_dot(ctx->tmap, ctx->tmap_x, static_cast<int32_t>(q_row),
-                                  static_cast<int32_t>(t_row), static_cast<int32_t>(x_row), tile % 4, d_out,
+    int r = sfm::launch_debug_dot(ctx->tmap, static_cast<int32_t>(q_row), static_cast<int32_t>(t_row), d_out,
                                   static_cast<cudaStream_t>(stream), &ctx->launches);
     if (r) return ctx->fail("debug launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     return 0;
@@ -947,7 +892,8 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (mode < 0 || mode > 15 || mode == 9) return ctx->fail("knn mode must be 0..8 or 10..15");
+    if (!(mode == 0 || mode == 1 || (mode >= 5 && mode <= 7) || (mode >= 12 && mode <= 15)))
+        return ctx->fail("knn mode must be 0, 1, 5..7 or 12..15");
     ctx->knn_mode = mode;
     return 0;
 }
@@ -979,35 +925,6 @@ int sfm_debug_handover_probe(sfm_ctx* ctx, int32_t iters, int32_t n_mma, int32_t
     if (r) return ctx->fail("probe launch failed: %s", cudaGetErrorString(static_cast<cudaError_t>(r)));
     SFM_CUDA(ctx, cudaMemcpyAsync(h_out4, ctx->d_meta.p, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     SFM_CUDA(ctx, cudaStreamSynchronize(st));
-    return 0;
-}
-
-int sfm_debug_knn_profile_events(sfm_ctx* ctx, int64_t* h_events, void* stream) {
-    if (!ctx || !h_events) return 1;
-    if (!ctx->d_prof.p) return ctx->fail("no profile recorded");
-    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
-    SFM_CUDA(ctx, cudaMemcpyAsync(h_events, ctx->d_prof.p + static_cast<size_t>(ctx->num_sms) * 16,
-                                  sizeof(long long) * 5 * 4096, cudaMemcpyDeviceToHost,
-                                  static_cast<cudaStream_t>(stream)));
-    SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
-    return 0;
-}
-
-int sfm_debug_knn_profile(sfm_ctx* ctx, int32_t enable, int64_t* h_sum16, void* stream) {
-    if (!ctx) return 1;
-    if (h_sum16) {
-        for (int i = 0; i < 16; ++i) h_sum16[i] = 0;
-        if (ctx->d_prof.p) {
-            SFM_CUDA(ctx, cudaSetDevice(ctx->device));
-            std::vector<long long> h(static_cast<size_t>(ctx->num_sms) * 16);
-            SFM_CUDA(ctx, cudaMemcpyAsync(h.data(), ctx->d_prof.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost,
-                                          static_cast<cudaStream_t>(stream)));
-            SFM_CUDA(ctx, cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
-            for (int b = 0; b < ctx->num_sms; ++b)
-                for (int i = 0; i < 16; ++i) h_sum16[i] += h[static_cast<size_t>(b) * 16 + i];
-        }
-    }
-    ctx->knn_prof = enable != 0;
     return 0;
 }
 

@@ -16,32 +16,29 @@ struct __align__(16) WorkItem {
     int32_t t_row;    // first row of the train image
     int32_t t_cnt;    // rows of the train image
     int32_t t_pad;    // offset of the train image in the 128-padded column-norm array
-    int32_t x_row;    // first row of the train image in the fold-step bias array (128-byte rows)
+    int32_t x_row;    // unused (kept for the 32-byte layout)
     int64_t out_row;  // first output row of this block in d_knn
 };
 static_assert(sizeof(WorkItem) == 32, "WorkItem must be 32 bytes");
 
-// ---- knn.cu
-// Bias array of the fold step: 128-byte rows; rows [0,128) are the constant A operand,
-// image i owns rows [x_off[i], x_off[i+1]) = 128 * ceil(n_i / 512).
+// ---- knn.cu (generic kNN kernel: the fallback for norms beyond the folded kernels' range; norms; work items)
 void launch_norms(const uint8_t* d_desc, int64_t total_rows, const int64_t* d_img_off,
-                  const int64_t* d_pad_off, const int64_t* d_x_off, int32_t n_images,
-                  int32_t* d_norms, int32_t* d_norms_pad, uint8_t* d_bias, int32_t* d_flags,
-                  cudaStream_t st, int64_t* launches);
+                  const int64_t* d_pad_off, int32_t n_images, int32_t* d_norms, int32_t* d_norms_pad,
+                  int32_t* d_flags, cudaStream_t st, int64_t* launches);
 void launch_build_work(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_blk_prefix,
                        const int64_t* d_row_off, const int64_t* d_img_off, const int64_t* d_pad_off,
-                       const int64_t* d_x_off, WorkItem* d_work, cudaStream_t st, int64_t* launches);
+                       WorkItem* d_work, cudaStream_t st, int64_t* launches);
 struct KnnTuning {
     uint32_t wait_ns = 0;         // mbarrier suspend hint of the producer / MMA warps (0 = spin; measured best)
     uint32_t epi_wait_ns = 0;     // same for the epilogue warps' accumulator-ready wait
     uint32_t probe_flags = 0;     // timing probes: bit 0 no B-tile TMA traffic, bit 1 no MMA issue
 };
-int launch_knn2(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc,
-                const WorkItem* d_work, int64_t n_work,
-                const int32_t* d_norms, const int32_t* d_norms_pad, int32_t* d_flags, int mode,
-                const KnnTuning& tn, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
-int launch_debug_dot(const CUtensorMap& tmap, const CUtensorMap& tmap_x, int32_t q_row, int32_t t_row,
-                     int32_t x_row, int32_t x_chunk, int32_t* d_out, cudaStream_t st, int64_t* launches);
+// only_if_flag != 0: exits at once unless flags[0] says a norm is beyond the folded kernels' range.
+int launch_knn2(const CUtensorMap& tmap, const WorkItem* d_work, int64_t n_work, const int32_t* d_norms,
+                const int32_t* d_norms_pad, const int32_t* d_flags, int only_if_flag, const KnnTuning& tn,
+                int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches);
+int launch_debug_dot(const CUtensorMap& tmap, int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st,
+                     int64_t* launches);
 int launch_mma_probe(int32_t iters, int32_t probe_n, int num_sms, cudaStream_t st, int64_t* launches);
 
 // ---- knn_wide.cu (N = 256 folded kernel; fold operands as u8 [128 + R, 32])
@@ -72,15 +69,9 @@ int launch_debug_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_ax, const u
 int launch_knn_fix(const WorkItem* d_work, int64_t n_work, const uint8_t* d_desc, const int32_t* d_norms,
                    const int32_t* d_flags, const int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms,
                    cudaStream_t st, int64_t* launches);
-// Norm parities of the padded column space as a bitmap (32 columns per word).
+// Norm parities of the padded column space as a bitmap (32 columns per word; knn_pair.cu).
 void launch_parity_bits(const int32_t* d_norms_pad, int64_t pad_total, uint32_t* d_par_bits, cudaStream_t st,
                         int64_t* launches);
-// TS kNN kernel: tmap = descriptor rows (128-row boxes), tmap_x = fold operand rows (32 B, 128-row boxes).
-int launch_knn2_ts(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const uint8_t* d_desc, const uint8_t* d_bias32,
-                   const WorkItem* d_work, int64_t n_work, const int32_t* d_norms, const int32_t* d_norms_pad,
-                   const uint32_t* d_par_bits, int32_t* d_flags, int variant, int force, const struct KnnTuning& tn,
-                   int32_t* d_fix_list, int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st,
-                   int64_t* launches, long long* d_prof = nullptr);
 // ---- knn_pair.cu (cta_group::2: a cluster of two CTAs per 256 query rows, four 128-column accumulator stages)
 // tmap_a = descriptor rows in 128-row boxes, tmap_b = the same array in 64-row boxes, tmap_x = fold operand rows
 // (32 B) in 64-row boxes, tmap_ax = the same array in a 128-row box (constant rows).

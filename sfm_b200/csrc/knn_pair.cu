@@ -747,6 +747,15 @@ debug_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
 }
 
+// Norm parities of the padded column space, one bit per column, 32 columns per word.
+__global__ void parity_bits_kernel(const int32_t* __restrict__ norms_pad, long long pad_total,
+                                   uint32_t* __restrict__ par_bits) {
+    const long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const bool odd = c < pad_total && (norms_pad[c] & 1);
+    const unsigned bal = __ballot_sync(0xffffffffu, odd);
+    if ((threadIdx.x & 31) == 0 && c < pad_total) par_bits[c >> 5] = bal;
+}
+
 template <int MODE>
 cudaError_t launch_pair_variant(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_x,
                                 const CUtensorMap& tmap_ax, const uint8_t* d_desc, const WorkItem* d_work,
@@ -767,6 +776,14 @@ cudaError_t launch_pair_variant(const CUtensorMap& tmap_a, const CUtensorMap& tm
 }
 
 }  // namespace
+
+void launch_parity_bits(const int32_t* d_norms_pad, int64_t pad_total, uint32_t* d_par_bits, cudaStream_t st,
+                        int64_t* launches) {
+    if (pad_total <= 0) return;
+    parity_bits_kernel<<<static_cast<unsigned>((pad_total + 255) / 256), 256, 0, st>>>(d_norms_pad, pad_total,
+                                                                                      d_par_bits);
+    ++*launches;
+}
 
 // variant 0: the kNN (exits at once when the fold-range flag is raised, unless force), followed by the
 // fix-up pass of knn_wide.cu; 1: max tree only, 2: no epilogue (timing probes).

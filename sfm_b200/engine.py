@@ -97,17 +97,18 @@ class PairEngine:
 
     # --------------------------------------------------------------- chunks
     def _chunks(self, pairs):
+        """(lo, hi) ranges of the pair list whose kNN rows fit the arenas (at least one pair each)."""
         rows = self.counts[pairs[:, 0]].astype(np.int64)
         if self.mutual and self._full_reverse():
             rows = np.maximum(rows, self.counts[pairs[:, 1]].astype(np.int64))
-        lo, acc = 0, 0
-        for p in range(len(pairs)):
-            if p > lo and acc + rows[p] > self.max_rows:
-                yield lo, p
-                lo, acc = p, 0
-            acc += rows[p]
-        if lo < len(pairs):
-            yield lo, len(pairs)
+        cum = np.cumsum(rows)
+        lo, n = 0, len(pairs)
+        while lo < n:
+            before = int(cum[lo - 1]) if lo else 0
+            hi = int(np.searchsorted(cum, before + self.max_rows, side="right"))
+            hi = min(max(hi, lo + 1), n)
+            yield lo, hi
+            lo = hi
 
     def _full_reverse(self) -> bool:
         if self.mutual_full:

@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_mutual_filter", "sfm_debug_fold_tile", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_knn_profile", "sfm_debug_knn_profile_events", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_mutual_filter", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -92,15 +92,12 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_dot_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_probe_int8_rate.argtypes = [vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
-    lib.sfm_debug_fold_tile.argtypes = [vp, i64, i32, i32, vp, vp]
     lib.sfm_debug_wide_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_ts_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_pair_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_pair_counters.argtypes = [vp, C.POINTER(i64), vp]
     lib.sfm_debug_ts_rate_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_set_knn_mode.argtypes = [vp, i32]
-    lib.sfm_debug_knn_profile.argtypes = [vp, i32, C.POINTER(i64), vp]
-    lib.sfm_debug_knn_profile_events.argtypes = [vp, vp, vp]
     lib.sfm_debug_handover_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i64), vp]
     lib.sfm_debug_set_knn_waits.argtypes = [vp, i32, i32]
     lib.sfm_debug_mma_handshake_probe.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_float), vp]
@@ -397,12 +394,6 @@ class Context:
         return out
 
 
-    def debug_fold_tile(self, q_row, train_image, tile):
-        out = self.empty((128, 128), self.torch.int32)
-        self._check(self.lib.sfm_debug_fold_tile(self.h, q_row, train_image, tile,
-                                                 self._dev(out, self.torch.int32), self._stream()))
-        return out
-
     def debug_wide_tile(self, q_row, t_row):
         out = self.empty((128, 256), self.torch.int32)
         self._check(self.lib.sfm_debug_wide_tile(self.h, q_row, t_row, self._dev(out, self.torch.int32),
@@ -440,27 +431,8 @@ class Context:
         per = {0: 4096, 1: 4096, 2: 8192, 3: 4096}[variant]
         return per * iters * warps / cyc.value, cyc.value
 
-    def knn_profile(self, enable: bool):
-        """Switch the TS kernel's profiling build on/off; returns the 16 cycle counters of the last
-        instrumented launch summed over the CTAs (see knn_ts.cu for the layout)."""
-        buf = (C.c_int64 * 16)()
-        self._check(self.lib.sfm_debug_knn_profile(self.h, int(enable), buf, self._stream()))
-        return [int(x) for x in buf]
-
-    def handover_probe(self, n_mma, tile_n=128, iters=256, trail=0):
-        """-> dict of mean cycles: issue, issue->other warp woken, arrive->issuer woken, issue->self woken."""
-        buf = (C.c_int64 * 4)()
-        self._check(self.lib.sfm_debug_handover_probe(self.h, iters, n_mma, tile_n, trail, buf, self._stream()))
-        return dict(issue=int(buf[0]), to_other_warp=int(buf[1]), plain_hop_back=int(buf[2]), to_self=int(buf[3]))
-
-    def knn_profile_events(self) -> np.ndarray:
-        """int64 [5, 4096]: time stamps (cycles) of CTA 0's first groups in the last instrumented launch."""
-        ev = np.zeros((5, 4096), np.int64)
-        self._check(self.lib.sfm_debug_knn_profile_events(self.h, _h(ev), self._stream()))
-        return ev
-
     def set_knn_mode(self, mode: int):
-        """0 auto, 1 generic, 2 folded, 3 folded fast path only (timing probe)."""
+        """0 auto, 1 generic, 5 wide, 12 CTA pair, 15 wide + skip; 6 / 7 / 13 / 14 timing probes (sfm_match.h)."""
         self._check(self.lib.sfm_debug_set_knn_mode(self.h, mode))
 
     def set_knn_waits(self, wait_ns: int, epi_wait_ns: int):

@@ -1,6 +1,6 @@
 """Same-box A/B of the kNN kernel variants (B200 box; not a pytest module):
-mode 5 wide (SS, 2 x 256-column accumulators), 8 TS (A in TMEM, 3 x 128), 6/10 their max-tree-only
-probes, 7/11 their no-epilogue probes.  Useful int8 TOP/s = 256 Nq Nt per pair / time."""
+mode 5 wide (2 x 256-column accumulators), 12 CTA pair (4 x 128), 15 wide + skip, 6/13 their max-tree-only
+probes, 7/14 their no-epilogue probes.  Useful int8 TOP/s = 256 Nq Nt per pair / time."""
 import json
 import sys
 from pathlib import Path
@@ -13,7 +13,7 @@ from sfm_b200 import lib as L, synth  # noqa: E402
 
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 n_desc = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
-modes = [int(m) for m in sys.argv[3].split(",")] if len(sys.argv) > 3 else [5, 8, 6, 10, 7, 11, 5, 8]
+modes = [int(m) for m in sys.argv[3].split(",")] if len(sys.argv) > 3 else [5, 12, 15, 6, 13, 7, 14, 5, 12]
 waits = [tuple(int(x) for x in w.split(":")) for w in sys.argv[4].split(",")] if len(sys.argv) > 4 else [(0, 0)]
 pflags = [int(x) for x in sys.argv[5].split(",")] if len(sys.argv) > 5 else [0]
 s = synth.make_image_set(n_img, n_desc, seed=synth.BASE_SEED + 1, device="cuda", tie_frac=0.01)
@@ -40,7 +40,7 @@ for mode, (w_ns, e_ns), pf in [(m, w, f) for m in modes for w in waits for f in 
         torch.cuda.synchronize()
         ts.append(round(ops / (e0.elapsed_time(e1) * 1e-3) / 1e12, 1))
     out.setdefault(f"mode{mode}_w{w_ns}_e{e_ns}_pf{pf}_tops", []).append(ts)
-    if mode in (5, 8) and pf == 0:
+    if mode in (5, 12, 15) and pf == 0:
         got = buf.clone()
         if ref is None:
             ref = got

@@ -2,7 +2,7 @@
 (utils/sfm_reconstruction.py: StructureFromMotion.run_reconstruction / save_reconstruction, as
 main.py:214-231 drives them) run on a preprocess output directory.
 
-    python tests/run_reference_reconstruct.py DATA_DIR [num_images]
+    python tests/run_reference_reconstruct.py DATA_DIR [num_images] [seed]
 
 Runs only where /root/reference exists (the build container, no GPU needed): DATA_DIR is either the
 reference's shipped bunny_data or the directory tests/make_bunny_outputs.py wrote with the B200
@@ -30,6 +30,7 @@ HARD_CODED = "/teamspace/studios/this_studio/SFM/bunny_data/matching_results.csv
 def main():
     data_dir = Path(sys.argv[1]).resolve()
     num_images = int(sys.argv[2]) if len(sys.argv) > 2 else 36
+    seed = int(sys.argv[3]) if len(sys.argv) > 3 else 0
     if not REF.exists():
         raise SystemExit("needs /root/reference")
     sys.path.insert(0, str(Path(__file__).resolve().parent / "stubs"))
@@ -50,9 +51,9 @@ def main():
     sys.path.insert(0, str(REF))
     scratch = tempfile.mkdtemp(prefix="sfm_recon_")
     os.chdir(scratch)
-    np.random.seed(0)
+    np.random.seed(seed)
     import cv2
-    cv2.setRNGSeed(0)
+    cv2.setRNGSeed(seed)
     from utils.sfm_reconstruction import StructureFromMotion
     t0 = time.perf_counter()
     sfm = StructureFromMotion(data_dir)

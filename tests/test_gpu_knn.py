@@ -196,25 +196,13 @@ def test_knn_32k_config_sample_vs_oracle_and_properties(ctx):
 
 
 # ---------------------------------------------------------------- kernel variants
-FOLD_C = 255 * 31 * 255 + 254          # sfm_b200/csrc/knn.cu kFoldC
+FOLD_C = 255 * 31 * 255 + 254          # sfm_b200/csrc/knn_wide.cu kFoldC
+
+
 def _sift_like(sizes, seed):
     from sfm_b200 import synth
     s = synth.make_image_set(len(sizes), list(sizes), seed=seed, tie_frac=0.03)
     return [s.image(i)[0].numpy() for i in range(len(sizes))]
-
-
-def test_fold_step_accumulators(ctx):
-    """The fifth K-step (u8 constants x u8 digits of C - floor(||b||^2/2)) through TMA + tcgen05:
-    accumulators must equal a.b + C - (||b||^2 >> 1) exactly (bias layout, digit encoding)."""
-    descs = _sift_like([300, 1500, 700], 31)
-    off = register(ctx, descs)
-    assert ctx.fold_flag() == 0
-    for q_img, q0, t_img, tile in [(0, 0, 1, 0), (0, 100, 1, 5), (2, 131, 1, 11), (1, 640, 2, 4), (1, 7, 0, 2)]:
-        got = ctx.debug_fold_tile(int(off[q_img]) + q0, t_img, tile).cpu().numpy()
-        a = descs[q_img][q0:q0 + 128].astype(np.int64)
-        b = descs[t_img][tile * 128:(tile + 1) * 128].astype(np.int64)
-        want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
-        assert np.array_equal(got[:len(a), :len(b)], want)
 
 
 def test_wide_fold_tile_accumulators(ctx):
@@ -229,6 +217,22 @@ def test_wide_fold_tile_accumulators(ctx):
         got = ctx.debug_wide_tile(q_row, t_row).cpu().numpy()
         a = allrows[q_row:q_row + 128]
         b = allrows[t_row:t_row + 256]
+        want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
+        assert np.array_equal(got[:len(a), :len(b)], want)
+
+
+def test_pair_fold_tile_accumulators(ctx):
+    """CTA-pair path (tcgen05.mma.cta_group::2, M = 256 over two CTAs, each staging its 128 query rows and
+    64 of the 128 train rows): accumulators of a 256 x 128 tile must equal a.b + C - (||b||^2 >> 1) exactly."""
+    descs = _sift_like([300, 1500, 700], 31)
+    off = register(ctx, descs)
+    total = int(off[-1])
+    allrows = np.concatenate(descs).astype(np.int64)
+    for q_row, t_row in [(0, 300), (100, 300 + 512), (1800 + 131, 300 + 1024), (300 + 640, 1800), (7, 0),
+                         (total - 256, total - 100)]:
+        got = ctx.debug_pair_tile(q_row, t_row).cpu().numpy()
+        a = allrows[q_row:q_row + 256]
+        b = allrows[t_row:t_row + 128]
         want = a @ b.T + FOLD_C - ((b * b).sum(1) >> 1)[None, :]
         assert np.array_equal(got[:len(a), :len(b)], want)
 
@@ -249,7 +253,7 @@ def test_ts_fold_tile_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
-@pytest.mark.parametrize("mode", [5, 8])
+@pytest.mark.parametrize("mode", [5, 12, 15])
 def test_knn_fixup_paths(ctx, mode):
     """Data made of few distinct descriptors: unit maxima tie everywhere, so the folded kernels'
     tied-unit recompute and their brute-force fix-up pass (list driven, and the overflow scan with the
@@ -273,7 +277,7 @@ def test_knn_fixup_paths(ctx, mode):
             check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-@pytest.mark.parametrize("mode", [5, 8])
+@pytest.mark.parametrize("mode", [5, 12, 15])
 def test_knn_long_train_images(ctx, mode):
     """Folded kernels with long train images (wide: beyond 8192 rows, TS: beyond 16384): unit ids need
     more than 8 key bits, the unit maxima are truncated in the packed keys and ties on the truncated
@@ -291,7 +295,7 @@ def test_knn_long_train_images(ctx, mode):
         check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-@pytest.mark.parametrize("mode", [1, 2, 5, 8])
+@pytest.mark.parametrize("mode", [1, 5, 12, 15])
 def test_knn_variants_match_oracle(ctx, mode):
     """Generic (1), N = 128 folded (2), wide folded (5) and TS (8) kernels, forced, on SIFT-like data
     with partial tiles and ties."""
