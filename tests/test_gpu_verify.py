@@ -111,7 +111,7 @@ def test_ransac_vs_reference_golden(ctx, bunny):
     assert np.median(jac) >= 0.95, np.median(jac)
     assert np.percentile(jac, 10) >= 0.85, np.percentile(jac, 10)
     assert np.median(errs) <= np.median(ref_errs) * 1.05
-    assert len(flips) <= 8, flips
+    assert len(flips) <= 2, flips        # observed: none (seed of the default params), at most 2 over other seeds
     print(f"\nRANSAC parity: jaccard median {np.median(jac):.3f} p10 {np.percentile(jac, 10):.3f} "
           f"min {jac.min():.3f}; dI median {np.median(dI):+.0f} min {min(dI):+d} max {max(dI):+d}; "
           f"gate flips {flips}; err median {np.median(errs):.3f} (ref {np.median(ref_errs):.3f})")
