@@ -1,10 +1,12 @@
-// Per-hypothesis mathematics of the fundamental-matrix RANSAC, written once
-// for device code (ransac.cu) and for the host build used by the CPU-side
-// algorithm tests (tests/hostsim/).  No reference code: OpenCV's
-// findFundamentalMat (reference call site utils/find_matches.py:282) is a
-// 7-point RANSAC with its own RNG; this is the normalised 8-point solve with
-// Sampson scoring named by the north star, with a counter-based RNG so that
-// the result is a pure function of (seed, pair key, correspondences).
+// Per-hypothesis mathematics of the fundamental-matrix RANSAC (device code of
+// ransac.cu; SFM_HD so that the same functions compile for the host).  No
+// reference code: OpenCV's findFundamentalMat (reference call site
+// utils/find_matches.py:282) is a 7-point RANSAC with its own RNG; this is the
+// normalised 8-point solve with a counter-based RNG, so that the result is a
+// pure function of (seed, pair key, correspondences).  Hypotheses are scored
+// with the symmetric epipolar error (OpenCV's own measure) or, by flag, with
+// the Sampson error the north star names (sfm_verify_params::score_mode: the
+// Sampson variant leaves the SURVEY 8c envelope on the golden pairs).
 #pragma once
 #include <cmath>
 #include <cstdint>
