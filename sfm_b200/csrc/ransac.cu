@@ -27,7 +27,10 @@ namespace sfm {
 
 namespace {
 
-constexpr int kThreads = 128;   // 4 CTAs per SM: the per-pair phases are latency chains, residency hides them
+// 128 threads, FOUR CTAs per SM (launch bound: 128 registers, 268 bytes of spills): the per-pair phases are
+// latency chains and residency hides them -- measured on the 200 x 8k workload: 3 CTAs (166 registers, no
+// spill) 15.6 ms, 4 CTAs 14.1 ms, 5 CTAs (96 registers, 840 bytes of spills) 15.7 ms.
+constexpr int kThreads = 128;
 constexpr int kWarps = kThreads / 32;
 constexpr int kChunk = 2048;   // staged correspondences per pass (32 KiB)
 constexpr int kMinSample = 8;
@@ -191,7 +194,7 @@ __device__ void write_skip(int p, int m, int status, long long base, uint8_t* ma
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, 4)
 ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32_t* __restrict__ cnt,
                      const int32_t* __restrict__ pair_ids, const float* __restrict__ pts1,
                      const float* __restrict__ pts2, const double* __restrict__ F_in,
