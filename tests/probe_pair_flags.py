@@ -4,7 +4,7 @@ from pathlib import Path
 import numpy as np, torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from sfm_b200 import lib as L, synth  # noqa: E402
-n_img = 12
+n_img = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 s = synth.make_image_set(n_img, 8192, seed=synth.BASE_SEED + 1, device="cuda", tie_frac=0.01)
 ctx = L.Context(0)
 ctx.set_images(s.desc, s.kps, s.offsets.numpy())
