@@ -232,6 +232,9 @@ SFM_API int64_t sfm_launch_count(sfm_ctx* ctx);
  * for `iters` 128x128x128 tile products per CTA and returns the elapsed
  * milliseconds (CUDA events) in *ms and the int8 op count in *ops. */
 SFM_API int sfm_probe_int8_peak(sfm_ctx* ctx, int32_t iters, float* ms, double* ops, void* stream);
+/* FP64 issue-rate probe (the bound of sfm_radius_match): eight independent DFMA chains per thread on every
+ * SM; *instr = thread-level f64 instructions executed, *ms = elapsed. */
+SFM_API int sfm_probe_fp64_rate(sfm_ctx* ctx, int32_t iters, float* ms, double* instr, void* stream);
 /* Same with 128 x tile_n x 128 tile products (tile_n = 64, 128 or 256; the peak probe uses 256):
  * shows how the shared-memory operand reads of narrower tiles hold the tensor pipe back. */
 SFM_API int sfm_probe_int8_rate(sfm_ctx* ctx, int32_t iters, int32_t tile_n, float* ms, double* ops,

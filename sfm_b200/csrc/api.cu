@@ -755,6 +755,32 @@ int sfm_probe_int8_rate(sfm_ctx* ctx, int32_t iters, int32_t tile_n, float* ms, 
     return 0;
 }
 
+int sfm_probe_fp64_rate(sfm_ctx* ctx, int32_t iters, float* ms, double* instr, void* stream) {
+    if (!ctx) return 1;
+    if (iters <= 0 || !ms || !instr) return ctx->fail("bad probe arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, ctx->d_meta.reserve(8));
+    cudaEvent_t e0, e1;
+    SFM_CUDA(ctx, cudaEventCreate(&e0));
+    SFM_CUDA(ctx, cudaEventCreate(&e1));
+    double* scratch = reinterpret_cast<double*>(ctx->d_meta.p);
+    int r = sfm::launch_fp64_probe(iters, ctx->num_sms, scratch, st, &ctx->launches);   // warm-up
+    if (!r) {
+        cudaEventRecord(e0, st);
+        r = sfm::launch_fp64_probe(iters, ctx->num_sms, scratch, st, &ctx->launches);
+        cudaEventRecord(e1, st);
+    }
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (!r && e == cudaSuccess) cudaEventElapsedTime(ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (r || e != cudaSuccess)
+        return ctx->fail("probe failed: %s", cudaGetErrorString(r ? static_cast<cudaError_t>(r) : e));
+    *instr = 8.0 * 512.0 * 4.0 * ctx->num_sms * static_cast<double>(iters);
+    return 0;
+}
+
 int sfm_debug_dot_tile(sfm_ctx* ctx, int64_t q_row, int64_t t_row, int32_t* d_out, void* stream) {
     if (!ctx) return 1;
     if (!ctx->have_tmap) return ctx->fail("no descriptors registered");

@@ -26,54 +26,70 @@ __device__ __forceinline__ bool ratio_pass(int d1, int d2, double ratio) {
     return static_cast<double>(s1) < ratio * static_cast<double>(s2);
 }
 
+// A block walks its pair in tiles of 4 x 256 query rows: every thread loads four rows (row = tile + 256 k + tid:
+// each load is one coalesced 4 KiB warp request), the 32 per-(k, warp) survivor counts go to shared memory, and
+// after ONE barrier every warp scans them itself with shuffles -- the running base lives in a register, the
+// count arrays alternate between tiles.  (Round 1 took three barriers per 256 rows: 34 % of the HBM peak.)
+constexpr int kRowsPerThread = 4;
+
 __global__ void __launch_bounds__(kThreads)
 filter_kernel(const int32_t* __restrict__ pairs, int n_pairs, const long long* __restrict__ img_off,
               const long long* __restrict__ row_off, const int4* __restrict__ knn,
               const long long* __restrict__ row_off_rev, const int4* __restrict__ knn_rev,
               double ratio, int32_t* __restrict__ mq, int32_t* __restrict__ mt,
               int32_t* __restrict__ md2, int32_t* __restrict__ count) {
-    __shared__ int warp_tot[kThreads / 32];
-    __shared__ int base_s;
+    __shared__ int wc[2][32];
+    static_assert(kRowsPerThread * (kThreads / 32) == 32, "one count per lane of the scanning warp");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int it = 0;
     for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
         const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
         const int nq = static_cast<int>(img_off[qi + 1] - img_off[qi]);
         const int nt = static_cast<int>(img_off[ti + 1] - img_off[ti]);
         const long long r0 = row_off[p];
         const int4* rev = knn_rev ? knn_rev + row_off_rev[p] : nullptr;
-        if (threadIdx.x == 0) base_s = 0;
-        __syncthreads();
-        for (int q0 = 0; q0 < nq; q0 += kThreads) {
-            const int q = q0 + threadIdx.x;
-            bool keep = false;
-            int4 r = make_int4(-1, -1, 0, 0);
-            if (q < nq && nt >= 2) {
-                r = __ldg(knn + r0 + q);
-                keep = r.x >= 0 && r.y >= 0 && ratio_pass(r.z, r.w, ratio);
-                if (keep && rev) keep = __ldg(&rev[r.x].x) == q;
-            }
-            const unsigned bal = __ballot_sync(0xffffffffu, keep);
-            if (lane == 0) warp_tot[warp] = __popc(bal);
-            __syncthreads();
-            int before = base_s, total = 0;
+        int base = 0;
+        for (int q0 = 0; q0 < nq; q0 += kRowsPerThread * kThreads, ++it) {
+            int4 r[kRowsPerThread];
+            bool keep[kRowsPerThread];
+            unsigned bal[kRowsPerThread];
 #pragma unroll
-            for (int w = 0; w < kThreads / 32; ++w) {
-                const int c = warp_tot[w];
-                if (w < warp) before += c;
-                total += c;
+            for (int k = 0; k < kRowsPerThread; ++k) {
+                const int q = q0 + k * kThreads + threadIdx.x;
+                r[k] = make_int4(-1, -1, 0, 0);
+                if (q < nq && nt >= 2) r[k] = __ldg(knn + r0 + q);
             }
-            if (keep) {
-                const long long o = r0 + before + __popc(bal & ((1u << lane) - 1u));
-                mq[o] = q;
-                mt[o] = r.x;
-                md2[o] = r.z;
+#pragma unroll
+            for (int k = 0; k < kRowsPerThread; ++k) {
+                const int q = q0 + k * kThreads + threadIdx.x;
+                keep[k] = r[k].x >= 0 && r[k].y >= 0 && ratio_pass(r[k].z, r[k].w, ratio);
+                if (keep[k] && rev) keep[k] = __ldg(&rev[r[k].x].x) == q;
+                bal[k] = __ballot_sync(0xffffffffu, keep[k]);
+                if (lane == 0) wc[it & 1][k * (kThreads / 32) + warp] = __popc(bal[k]);
             }
             __syncthreads();
-            if (threadIdx.x == 0) base_s += total;
-            __syncthreads();
+            const int x = wc[it & 1][lane];
+            int incl = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            const int excl = incl - x;
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+            for (int k = 0; k < kRowsPerThread; ++k) {
+                const int before = __shfl_sync(0xffffffffu, excl, k * (kThreads / 32) + warp);
+                if (keep[k]) {
+                    const long long o = r0 + base + before + __popc(bal[k] & ((1u << lane) - 1u));
+                    mq[o] = q0 + k * kThreads + threadIdx.x;
+                    mt[o] = r[k].x;
+                    md2[o] = r[k].z;
+                }
+            }
+            base += total;
         }
-        if (threadIdx.x == 0) count[p] = base_s;
-        __syncthreads();
+        if (threadIdx.x == 0) count[p] = base;
     }
 }
 

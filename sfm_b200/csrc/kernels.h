@@ -91,6 +91,9 @@ int launch_ts_rate_probe(int groups, int tile_n, int ts, int commit, int num_sms
 int launch_tmem_ld_probe(int warps, int variant, int iters, int num_sms, long long* d_out, cudaStream_t st,
                          int64_t* launches);
 
+// FP64 DFMA issue-rate probe: num_sms * 4 CTAs x 512 threads x 8 chains x iters instructions.
+int launch_fp64_probe(int iters, int num_sms, double* d_out, cudaStream_t st, int64_t* launches);
+
 int launch_mma_handshake_probe(int steps, int k_per_acc, int flags, int consumers, int num_sms,
                                cudaStream_t st, int64_t* launches);
 

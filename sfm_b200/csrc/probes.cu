@@ -226,4 +226,29 @@ int launch_tmem_ld_probe(int warps, int variant, int iters, int num_sms, long lo
     return static_cast<int>(cudaGetLastError());
 }
 
+namespace {
+// FP64 instruction-rate probe: eight independent DFMA chains per thread, 1024 threads per SM x 2 CTAs.
+// The radius matcher (radius.cu) is bound by the FP64 pipe's ISSUE rate (its DADD / DMUL count one each).
+__global__ void __launch_bounds__(512) fp64_probe_kernel(int iters, double seed, double* __restrict__ out) {
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = seed + i + threadIdx.x;
+    const double a = 1.0000001, b = 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = fma(x[i], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[i];
+    if (s == 12345.678) out[0] = s;   // keeps the chains live
+}
+}  // namespace
+
+int launch_fp64_probe(int iters, int num_sms, double* d_out, cudaStream_t st, int64_t* launches) {
+    fp64_probe_kernel<<<num_sms * 4, 512, 0, st>>>(iters, 0.5, d_out);
+    ++*launches;
+    return static_cast<int>(cudaGetLastError());
+}
+
 }  // namespace sfm

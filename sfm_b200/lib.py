@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_mutual_filter", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_mutual_filter", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_probe_fp64_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -92,6 +92,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_probe_int8_peak.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_dot_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_probe_int8_rate.argtypes = [vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
+    lib.sfm_probe_fp64_rate.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(C.c_double), vp]
     lib.sfm_debug_wide_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_ts_tile.argtypes = [vp, i64, i64, vp, vp]
     lib.sfm_debug_pair_tile.argtypes = [vp, i64, i64, vp, vp]
@@ -430,6 +431,12 @@ class Context:
         self._check(self.lib.sfm_debug_tmem_ld_probe(self.h, warps, variant, iters, C.byref(cyc), self._stream()))
         per = {0: 4096, 1: 4096, 2: 8192, 3: 4096}[variant]
         return per * iters * warps / cyc.value, cyc.value
+
+    def probe_fp64_rate(self, iters=4096):
+        """-> f64 instructions per second of an all-SM DFMA loop (the radius matcher's roofline)."""
+        ms, n = C.c_float(), C.c_double()
+        self._check(self.lib.sfm_probe_fp64_rate(self.h, iters, C.byref(ms), C.byref(n), self._stream()))
+        return n.value / (ms.value * 1e-3)
 
     def set_knn_mode(self, mode: int):
         """0 auto, 1 generic, 5 wide, 12 CTA pair, 15 wide + skip; 6 / 7 / 13 / 14 timing probes (sfm_match.h)."""

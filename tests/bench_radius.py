@@ -64,14 +64,16 @@ def main():
     # 4 more for the ~0.4 % inside the x band), none of them an FMA; the fill pass copies kept hits.
     # The FP64 pipe issues one instruction per FMA slot: instruction peak = nominal 37 TFLOP/s / 2.
     flops = 3 * tests / (ms * 1e-3)
+    peak = ctx.probe_fp64_rate(8192) / 1e12      # measured: all-SM DFMA loop, T f64 instructions/s
     print(json.dumps({
         "metric": "track_point_tests_per_sec", "value": tests / (ms * 1e-3), "unit": "tests/s", "ms": ms,
         "workload": f"{n_seg} segments x {nt} tracks x {npnt} points, threshold 2.0", "hits": int(so[-1]),
         "gpu_launches_per_call": int(launches),
         "e2e": {"value": tests / (e2e_ms * 1e-3), "unit": "tests/s", "ms": e2e_ms,
                 "h2d_bytes": int(tracks.nbytes + pts.nbytes), "d2h_bytes": int(8 * so[-1] + so.nbytes)},
-        "roofline": {"bound": "fp64 pipe", "achieved": flops / 1e12, "peak": 18.5, "unit": "T f64 instr/s",
-                     "frac": flops / 1e12 / 18.5,
+        "roofline": {"bound": "fp64 pipe", "achieved": flops / 1e12, "peak": peak, "unit": "T f64 instr/s",
+                     "frac": flops / 1e12 / peak, "frac_of_nominal_18.5": flops / 1e12 / 18.5,
+                     "peak_source": "measured in this run: sfm_probe_fp64_rate (eight DFMA chains per thread on every SM)",
                      "note": "sub, mul, compare per test, the rest only inside the x band (no FMA: each step rounds as numpy "
                              "does); the ms include the scan, the offset read-back and the fill pass; "
                              "peak = nominal B200 FP64 37 TFLOP/s / 2 flops per FMA slot"},
