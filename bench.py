@@ -79,16 +79,21 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_indices):
+        """gpu_indices: the GPUs to watch with ONE nvidia-smi process ('' or None: no sampling in this process).
+        Under torchrun only rank 0 samples, all GPUs of the job: eight pollers on one box stalled the kernel
+        launches of every rank for 50-100 ms at a time (one outlier step per run at N = 8)."""
         self.rows = []
         self.proc = None
-        self.idx = gpu_index
+        self.idx = ",".join(str(i) for i in gpu_indices) if gpu_indices else ""
 
     def __enter__(self):
+        if not self.idx:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
-                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-i", self.idx], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -325,7 +330,7 @@ def run_b200(args):
 
     # ---------------------------------------------------------- device-resident steps
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local_rank) as clk:               # started before the warm-up so that it is polling by now
+    with ClockSampler(list(range(world)) if rank == 0 else None) as clk:               # started before the warm-up so that it is polling by now
         for _ in range(args.warmup):
             eng.match_device(my_pairs)
         launches0 = eng.ctx.launches
@@ -381,7 +386,7 @@ def run_b200(args):
         k_tops = k_ops / (k_ms * 1e-3) / 1e12
         probe_tops, _ = eng.ctx.probe_int8_peak(4096)
         t_wait = time.perf_counter()
-        while len(clk.rows) < 5 and time.perf_counter() - t_wait < 6.0:   # short runs: let the sampler see the load
+        while clk.proc is not None and len(clk.rows) < 5 * world and time.perf_counter() - t_wait < 6.0:   # short runs: let the sampler see the load
             eng.ctx.knn2(kp, ro, kbuf)
             torch.cuda.synchronize()
     clocks = dict(clk.summary(), window="timed steps + stage split + kernel-alone region")
