@@ -302,7 +302,7 @@ SFM_API int sfm_debug_handover_probe(sfm_ctx* ctx, int32_t iters, int32_t n_mma,
 SFM_API int sfm_debug_fold_flag(sfm_ctx* ctx, int32_t* h_flag, void* stream);
 
 /* Statistics: query rows the folded kNN kernel recomputed by brute force since the last
- * sfm_set_images (rows whose candidate tracking met an exact tie; see knn.cu).  Synchronises. */
+ * sfm_set_images (rows whose candidate tracking met an exact tie; see knn_wide.cu).  Synchronises. */
 SFM_API int sfm_debug_brute_rows(sfm_ctx* ctx, int32_t* h_rows, void* stream);
 
 #ifdef __cplusplus
