@@ -35,6 +35,7 @@ extern "C" {
 #define SFM_DESC_DIM 128          /* SIFT descriptor length, bytes per row */
 #define SFM_QBLOCK 256            /* query rows per work item of the kNN kernel */
 #define SFM_TTILE 128             /* train rows per tensor-core tile */
+#define SFM_FILTER_STATIC_MAX_PAIRS 16384   /* most pairs per sfm_filter_matches_static call */
 
 typedef struct sfm_ctx sfm_ctx;
 
@@ -135,6 +136,27 @@ SFM_API int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_p
                        const int64_t* h_row_off_rev, const int32_t* d_knn_rev,
                        double ratio, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2,
                        int32_t* d_count, void* stream);
+
+/* sfm_filter_matches without allocation.  No counterpart in the reference: added
+ * for callers that may not call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same rule, same outputs and same argument meaning as
+ * sfm_filter_matches with d_knn_rev = NULL (ratio test only), bit for bit.  The per-call metadata
+ * (16 bytes per pair) is staged in a file-scope __device__ array of SFM_FILTER_STATIC_MAX_PAIRS
+ * records (256 KiB, held by every GPU that loads the library until the process exits) instead of
+ * buffers that grow with cudaMalloc / cudaMallocHost: the call makes no cudaMalloc, cudaFree,
+ * cudaMallocHost or other allocating call.  n_pairs beyond the maximum is rejected (return 1,
+ * sfm_last_error names the limit): split the batch, or use sfm_filter_matches.
+ * The array is shared by every call on the device.  Each call rewrites the records it reads, so
+ * nothing has to be cleared between calls; calls that OVERLAP ON THE GPU (different streams, or
+ * threads on one device) race on it -- order them on one stream or with an event.  The first call
+ * on a device resolves the array's address (cudaGetSymbolAddress; with lazy module loading this
+ * loads the kernel image): a call with n_pairs = 0 does only that and is the warm-up to make
+ * before graph capture.  The metadata copy reads pageable host memory, so the call returns after
+ * the stream's earlier work has been reached (it does not synchronise on its own kernel). */
+SFM_API int sfm_filter_matches_static(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
+                              const int64_t* h_row_off, const int32_t* d_knn, double ratio,
+                              int32_t* d_mq, int32_t* d_mt, int32_t* d_md2, int32_t* d_count,
+                              void* stream);
 
 /* ---- K3 + K4: RANSAC fundamental matrix + geometric verification ------ */
 /* Mutual nearest-neighbour check on match lists that have passed the ratio test (README.md:108 of the

@@ -12,7 +12,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libsfm_match.so"
 STAMP = PKG / ".libsfm_match.stamp"
-SOURCES = ["api.cu", "knn.cu", "knn_wide.cu", "knn_ts.cu", "knn_pair.cu", "filter.cu", "ransac.cu", "radius.cu", "probes.cu"]
+SOURCES = ["api.cu", "knn.cu", "knn_wide.cu", "knn_ts.cu", "knn_pair.cu", "filter.cu", "filter_static.cu", "ransac.cu", "radius.cu", "probes.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",

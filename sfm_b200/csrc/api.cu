@@ -460,6 +460,27 @@ int sfm_filter_matches(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs,
     return 0;
 }
 
+int sfm_filter_matches_static(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
+                              const int32_t* d_knn, double ratio, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2,
+                              int32_t* d_count, void* stream) {
+    if (!ctx) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_pairs(ctx, h_pairs, n_pairs)) return 1;
+    if (n_pairs > SFM_FILTER_STATIC_MAX_PAIRS)
+        return ctx->fail("n_pairs = %d exceeds SFM_FILTER_STATIC_MAX_PAIRS = %d (static scratch, no allocation): "
+                         "split the batch or call sfm_filter_matches",
+                         n_pairs, SFM_FILTER_STATIC_MAX_PAIRS);
+    if (n_pairs > 0 && (!h_row_off || !d_knn || !d_mq || !d_mt || !d_md2 || !d_count))
+        return ctx->fail("NULL argument");
+    if (n_pairs > 0 && ctx->h_off.size() != static_cast<size_t>(ctx->n_images) + 1)
+        return ctx->fail("no image set registered");
+    SFM_CUDA(ctx, cudaSetDevice(ctx->device));
+    SFM_CUDA(ctx, sfm::launch_filter_static(ctx->device, h_pairs, n_pairs, ctx->h_off.data(), h_row_off,
+                                            reinterpret_cast<const int4*>(d_knn), ratio, d_mq, d_mt, d_md2,
+                                            d_count, st, &ctx->launches));
+    return 0;
+}
+
 int sfm_mutual_filter(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_row_off,
                       const int32_t* h_count, int32_t* d_mq, int32_t* d_mt, int32_t* d_md2, int32_t* d_count,
                       void* stream) {

@@ -113,6 +113,14 @@ void launch_filter(const int32_t* d_pairs, int32_t n_pairs, const int64_t* d_img
                    const int4* d_knn_rev, double ratio, int32_t* d_mq, int32_t* d_mt,
                    int32_t* d_md2, int32_t* d_count, cudaStream_t st, int64_t* launches);
 
+// ---- filter_static.cu: the ratio filter with its metadata in a file-scope __device__ array (no allocation).
+// h_img_off: the registered image offsets (host).  Returns cudaErrorInvalidValue beyond
+// SFM_FILTER_STATIC_MAX_PAIRS; n_pairs == 0 only resolves the array's address for `device` (must be current).
+cudaError_t launch_filter_static(int device, const int32_t* h_pairs, int32_t n_pairs, const int64_t* h_img_off,
+                                 const int64_t* h_row_off, const int4* d_knn, double ratio, int32_t* d_mq,
+                                 int32_t* d_mt, int32_t* d_md2, int32_t* d_count, cudaStream_t st,
+                                 int64_t* launches);
+
 struct PackArrays {
     const int32_t *mq, *mt, *md2;
     const uint8_t* mask;

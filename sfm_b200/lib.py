@@ -46,7 +46,7 @@ EXPORTS = (
     "sfm_create", "sfm_destroy", "sfm_last_error", "sfm_default_params", "sfm_abi_version",
     "sfm_set_images", "sfm_knn2", "sfm_filter_matches", "sfm_verify_pairs", "sfm_verify_given_F",
     "sfm_ransac_points", "sfm_pack_results", "sfm_radius_match", "sfm_launch_count", "sfm_probe_int8_peak", "sfm_debug_dot_tile",
-    "sfm_mutual_filter", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_probe_fp64_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
+    "sfm_mutual_filter", "sfm_filter_matches_static", "sfm_debug_wide_tile", "sfm_debug_ts_tile", "sfm_debug_pair_tile", "sfm_debug_pair_counters", "sfm_debug_ts_rate_probe", "sfm_debug_handover_probe", "sfm_debug_set_knn_mode", "sfm_debug_fold_flag", "sfm_debug_tmem_ld_probe", "sfm_debug_set_knn_waits", "sfm_probe_int8_rate", "sfm_probe_fp64_rate", "sfm_debug_mma_handshake_probe", "sfm_debug_brute_rows", "sfm_debug_set_knn_probe_flags",
 )
 
 _lib = None
@@ -78,6 +78,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.sfm_set_images.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.sfm_knn2.argtypes = [vp, vp, i32, vp, vp, vp]
     lib.sfm_filter_matches.argtypes = [vp, vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp, vp, vp]
+    lib.sfm_filter_matches_static.argtypes = [vp, vp, i32, vp, vp, dbl, vp, vp, vp, vp, vp]
     lib.sfm_mutual_filter.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.sfm_verify_pairs.argtypes = [vp, vp, i32, vp, vp, vp, vp, C.POINTER(VerifyParams),
                                      vp, vp, vp, vp, vp, vp, vp, vp]
@@ -266,6 +267,23 @@ class Context:
             self._dev(knn_rev, torch.int32) if knn_rev is not None else C.c_void_p(0),
             float(ratio), self._dev(mq, torch.int32), self._dev(mt, torch.int32),
             self._dev(md2, torch.int32), self._dev(cnt, torch.int32), self._stream()))
+        return mq, mt, md2, cnt
+
+    def filter_matches_static(self, pairs, row_off, knn, ratio=0.75, out=None):
+        """sfm_filter_matches_static: the ratio filter with its metadata in the library's static device
+        array (the C entry point allocates nothing; pass `out` to keep this wrapper from allocating too)."""
+        torch = self.torch
+        pairs = _pairs(pairs)
+        row_off = _i64(row_off)
+        n = int(row_off[-1]) if len(row_off) else 0
+        if out is None:
+            out = (self.empty((n,), torch.int32), self.empty((n,), torch.int32),
+                   self.empty((n,), torch.int32), self.empty((len(pairs),), torch.int32))
+        mq, mt, md2, cnt = out
+        self._check(self.lib.sfm_filter_matches_static(
+            self.h, _h(pairs), len(pairs), _h(row_off), self._dev(knn, torch.int32), float(ratio),
+            self._dev(mq, torch.int32), self._dev(mt, torch.int32), self._dev(md2, torch.int32),
+            self._dev(cnt, torch.int32), self._stream()))
         return mq, mt, md2, cnt
 
     # -- K3 + K4
