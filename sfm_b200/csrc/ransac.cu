@@ -110,10 +110,98 @@ __device__ __forceinline__ float symmetric_error(const double (&F)[9], float x1,
     return __fmul_rn(__fadd_rn(e1, e2), 0.5f);
 }
 
-// refit_from_normal (ransac_core.h) with the 9x9 cyclic Jacobi run by one warp: the same rotation
-// sequence and the same arithmetic per element, lane k updating row/column entry k of A and lane
-// 9 + k that of V, instead of one thread walking dynamically indexed local arrays (that serial
-// eigen-solve was 40 % of the kernel).  Called by warp 0 only; result in F (all lanes).
+// (c, s) of the Jacobi rotation that annihilates a_pq, t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)) with
+// theta = (a_qq - a_pp) / (2 a_pq), written with one square root, one division and one reciprocal square
+// root: t = +-2 a_pq / (|d| + sqrt(d^2 + 4 a_pq^2)), c = rsqrt(t^2 + 1).  (The textbook form costs three
+// divisions and two square roots, each a dependent chain of ~200-300 cycles in double precision; the
+// eigen-solves of the refits are pure latency.)
+__device__ __forceinline__ void jacobi_cs(double app, double aqq, double apq, double& c, double& s) {
+    c = 1.0;
+    s = 0.0;
+    if (apq == 0.0) return;
+    const double d = aqq - app;
+    const double h = fabs(d) + sqrt(d * d + 4.0 * apq * apq);
+    if (!(h > 0.0)) return;                      // NaN, or d = 0 with a_pq^2 underflowing: nothing to rotate
+    double t = (apq + apq) / h;
+    if (d < 0.0) t = -t;
+    c = rsqrt(t * t + 1.0);
+    s = t * c;
+}
+
+// rc::smallest_eigvec3<double> with the rotation above and a convergence test (the generic version always
+// runs 8 sweeps = 24 rotations).
+__device__ void smallest_eigvec3_d(double a00, double a01, double a02, double a11, double a12, double a22,
+                                   double (&v)[3]) {
+    double A[3][3] = {{a00, a01, a02}, {a01, a11, a12}, {a02, a12, a22}};
+    double V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+#pragma unroll 1
+    for (int sweep = 0; sweep < 10; ++sweep) {
+        const double off = A[0][1] * A[0][1] + A[0][2] * A[0][2] + A[1][2] * A[1][2];
+        const double diag = A[0][0] * A[0][0] + A[1][1] * A[1][1] + A[2][2] * A[2][2];
+        if (off <= 1e-32 * diag) break;
+#pragma unroll
+        for (int pq = 0; pq < 3; ++pq) {
+            const int p = pq == 2 ? 1 : 0;
+            const int q = pq == 0 ? 1 : 2;
+            double c, s;
+            jacobi_cs(A[p][p], A[q][q], A[p][q], c, s);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double akp = A[k][p], akq = A[k][q];
+                A[k][p] = c * akp - s * akq;
+                A[k][q] = s * akp + c * akq;
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double apk = A[p][k], aqk = A[q][k];
+                A[p][k] = c * apk - s * aqk;
+                A[q][k] = s * apk + c * aqk;
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double vkp = V[k][p], vkq = V[k][q];
+                V[k][p] = c * vkp - s * vkq;
+                V[k][q] = s * vkp + c * vkq;
+            }
+        }
+    }
+    int m = 0;
+    if (A[1][1] < A[m][m]) m = 1;
+    if (A[2][2] < A[m][m]) m = 2;
+    v[0] = m == 0 ? V[0][0] : (m == 1 ? V[0][1] : V[0][2]);
+    v[1] = m == 0 ? V[1][0] : (m == 1 ? V[1][1] : V[1][2]);
+    v[2] = m == 0 ? V[2][0] : (m == 1 ? V[2][1] : V[2][2]);
+}
+
+// rc::enforce_rank2<double> on the eigen-solver above: F - (F v3) v3^T.
+__device__ void enforce_rank2_d(double (&F)[9]) {
+    double g[6];
+    g[0] = F[0] * F[0] + F[3] * F[3] + F[6] * F[6];
+    g[1] = F[0] * F[1] + F[3] * F[4] + F[6] * F[7];
+    g[2] = F[0] * F[2] + F[3] * F[5] + F[6] * F[8];
+    g[3] = F[1] * F[1] + F[4] * F[4] + F[7] * F[7];
+    g[4] = F[1] * F[2] + F[4] * F[5] + F[7] * F[8];
+    g[5] = F[2] * F[2] + F[5] * F[5] + F[8] * F[8];
+    double v[3];
+    smallest_eigvec3_d(g[0], g[1], g[2], g[3], g[4], g[5], v);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const double fv = F[3 * r] * v[0] + F[3 * r + 1] * v[1] + F[3 * r + 2] * v[2];
+        F[3 * r] -= fv * v[0];
+        F[3 * r + 1] -= fv * v[1];
+        F[3 * r + 2] -= fv * v[2];
+    }
+}
+
+// refit_from_normal (ransac_core.h) with the 9x9 Jacobi eigen-solve run by one warp in PARALLEL ORDER:
+// a sweep is nine rounds of four rotations in disjoint planes (round-robin pairing of the nine indices,
+// index r sits out in round r), the four (c, s) pairs are computed side by side by the lanes' groups
+// (lane & 3) and applied together: first the column pairs of A and V (36 + 36 element pairs over the
+// lanes), then the row pairs of A.  Rotations in disjoint planes commute, so this is the cyclic Jacobi
+// method with another visiting order: the scalar chain (sqrt, division, rsqrt: ~700 cycles) is paid 9
+// times per sweep instead of 36.  Round 1 ran the 36 rotations of a sweep one after the other: with two
+// refits per pair that serial eigen-solve was half of the kernel (12.4 ms with, 5.8 ms without refits
+// on the 19,900 pairs of the 200 x 8k set).  Called by warp 0 only; result in F (all lanes).
 __device__ bool warp_refit_from_normal(const double (&ata)[45], double c1x, double c1y, double s1, double c2x,
                                        double c2y, double s2, Shared& sh, double (&F)[9]) {
     const int lane = threadIdx.x & 31;
@@ -124,45 +212,50 @@ __device__ bool warp_refit_from_normal(const double (&ata)[45], double c1x, doub
         sh.jV[i][j] = i == j ? 1.0 : 0.0;
     }
     __syncwarp();
+    const int g = lane & 3, k0 = lane >> 2;
     for (int sweep = 0; sweep < 12; ++sweep) {
+        // squared norms of the strict upper triangle and of the diagonal: row `lane`, then a butterfly
         double off = 0, diag = 0;
-        for (int i = 0; i < 9; ++i) {
-            diag += sh.jA[i][i] * sh.jA[i][i];
-            for (int j = i + 1; j < 9; ++j) off += sh.jA[i][j] * sh.jA[i][j];
+        if (lane < 9) {
+            diag = sh.jA[lane][lane] * sh.jA[lane][lane];
+            for (int j = lane + 1; j < 9; ++j) off += sh.jA[lane][j] * sh.jA[lane][j];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            off += __shfl_xor_sync(0xffffffffu, off, o);
+            diag += __shfl_xor_sync(0xffffffffu, diag, o);
         }
         if (off <= 1e-30 * diag) break;
-        for (int p = 0; p < 8; ++p)
-            for (int q = p + 1; q < 9; ++q) {
-                const double apq = sh.jA[p][q];
-                if (apq == 0.0) continue;
-                const double theta = (sh.jA[q][q] - sh.jA[p][p]) / (2.0 * apq);
-                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
-                __syncwarp();
-                if (lane < 9) {
-                    const double akp = sh.jA[lane][p], akq = sh.jA[lane][q];
-                    sh.jA[lane][p] = c * akp - s * akq;
-                    sh.jA[lane][q] = s * akp + c * akq;
-                } else if (lane < 18) {
-                    const int k = lane - 9;
-                    const double vkp = sh.jV[k][p], vkq = sh.jV[k][q];
-                    sh.jV[k][p] = c * vkp - s * vkq;
-                    sh.jV[k][q] = s * vkp + c * vkq;
-                }
-                __syncwarp();
-                if (lane < 9) {
-                    const double apk = sh.jA[p][lane], aqk = sh.jA[q][lane];
-                    sh.jA[p][lane] = c * apk - s * aqk;
-                    sh.jA[q][lane] = s * apk + c * aqk;
-                }
-                __syncwarp();
+        for (int r = 0; r < 9; ++r) {
+            int a = r + 1 + g, b = r + 8 - g;          // (r + i) mod 9 and (r - i) mod 9, i = g + 1
+            a = a >= 9 ? a - 9 : a;
+            b = b >= 9 ? b - 9 : b;
+            const int p = a < b ? a : b, q = a < b ? b : a;
+            double c, s;
+            jacobi_cs(sh.jA[p][p], sh.jA[q][q], sh.jA[p][q], c, s);
+            __syncwarp();
+            for (int k = k0; k < 9; k += 8) {           // A <- A J, V <- V J: columns p, q of row k
+                const double akp = sh.jA[k][p], akq = sh.jA[k][q];
+                sh.jA[k][p] = c * akp - s * akq;
+                sh.jA[k][q] = s * akp + c * akq;
+                const double vkp = sh.jV[k][p], vkq = sh.jV[k][q];
+                sh.jV[k][p] = c * vkp - s * vkq;
+                sh.jV[k][q] = s * vkp + c * vkq;
             }
+            __syncwarp();
+            for (int k = k0; k < 9; k += 8) {           // A <- J^T A: rows p, q of column k
+                const double apk = sh.jA[p][k], aqk = sh.jA[q][k];
+                sh.jA[p][k] = c * apk - s * aqk;
+                sh.jA[q][k] = s * apk + c * aqk;
+            }
+            __syncwarp();
+        }
     }
     int m = 0;
     for (int i = 1; i < 9; ++i)
         if (sh.jA[i][i] < sh.jA[m][m]) m = i;
     for (int i = 0; i < 9; ++i) F[i] = sh.jV[i][m];
-    rc::enforce_rank2<double>(F);
+    enforce_rank2_d(F);
     rc::denormalise<double>(F, c1x, c1y, s1, c2x, c2y, s2);
     rc::scale_unit<double>(F);
     bool ok = true;
@@ -430,7 +523,7 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
             if (threadIdx.x == 0) {
                 double Fn[9];
                 for (int i = 0; i < 9; ++i) Fn[i] = sh.Fd[i];
-                rc::enforce_rank2<double>(Fn);     // exact rank 2 in float64
+                enforce_rank2_d(Fn);               // exact rank 2 in float64
                 rc::normalise_f22(Fn);
                 for (int i = 0; i < 9; ++i) sh.Fd[i] = Fn[i];
             }
