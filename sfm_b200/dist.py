@@ -63,40 +63,70 @@ def partition_pairs(pairs: np.ndarray, counts: np.ndarray, world: int):
     return [(int(cuts[r]), int(cuts[r + 1])) for r in range(world)]
 
 
-def _all_gather_var(t: torch.Tensor, group=None):
-    """all-gather of tensors whose first dimension differs per rank.
-    Returns the list of per-rank tensors (on t's device)."""
+def _gather_sizes(values, device, group=None) -> np.ndarray:
+    """int64 vector `values` of every rank as a [world, len(values)] host array: one collective, one host read."""
     world = dist.get_world_size(group)
-    n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
-    sizes = [torch.zeros_like(n) for _ in range(world)]
-    dist.all_gather(sizes, n, group=group)
-    sizes = [int(s.item()) for s in sizes]
-    mx = max(max(sizes), 1)
-    pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
-    pad[: t.shape[0]] = t
-    out = torch.empty((world * mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    mine = torch.tensor([int(v) for v in values], dtype=torch.int64, device=device)
+    out = torch.empty((world * mine.numel(),), dtype=torch.int64, device=device)
     if dist.get_backend(group) == "nccl":
-        dist.all_gather_into_tensor(out, pad, group=group)     # one ncclAllGather
+        dist.all_gather_into_tensor(out, mine, group=group)
+    else:
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        out = torch.cat(parts)
+    return out.cpu().numpy().reshape(world, -1)
+
+
+def _all_gather_rows(t: torch.Tensor, sizes, group=None):
+    """all-gather of tensors whose first dimension is sizes[rank] (known on every rank): the concatenation in
+    rank order.  Equal sizes -- the usual case, equal image blocks -- take one ncclAllGather straight into the
+    result; ragged sizes are padded to the largest block and the pieces concatenated."""
+    world = dist.get_world_size(group)
+    sizes = [int(x) for x in sizes]
+    mx = max(max(sizes), 1)
+    tail = tuple(t.shape[1:])
+    nccl = dist.get_backend(group) == "nccl"
+    if nccl and min(sizes) == mx:
+        out = torch.empty((world * mx,) + tail, dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t.contiguous(), group=group)
+        return out
+    pad = t
+    if t.shape[0] != mx:
+        pad = torch.zeros((mx,) + tail, dtype=t.dtype, device=t.device)
+        pad[: t.shape[0]] = t
+    if nccl:
+        out = torch.empty((world * mx,) + tail, dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, pad.contiguous(), group=group)     # one ncclAllGather
         parts = list(out.split(mx))
     else:
         parts = [torch.empty_like(pad) for _ in range(world)]
-        dist.all_gather(parts, pad, group=group)
-    return [p[:s] for p, s in zip(parts, sizes)]
+        dist.all_gather(parts, pad.contiguous(), group=group)
+    return torch.cat([p[:n] for p, n in zip(parts, sizes)])
+
+
+def _all_gather_var(t: torch.Tensor, group=None):
+    """all-gather of tensors whose first dimension differs per rank.
+    Returns the list of per-rank tensors (on t's device)."""
+    sizes = _gather_sizes([t.shape[0]], t.device, group)[:, 0]
+    cat = _all_gather_rows(t, sizes, group)
+    return list(cat.split([int(n) for n in sizes]))
 
 
 def replicate_images(local_desc: torch.Tensor, local_kps: torch.Tensor, local_counts, group=None):
     """Every rank contributes the descriptors/keypoints of its contiguous image
     block; returns the full (desc u8 [R,128], kps f32 [R,2], offsets int64 [N+1])
-    on every rank, in image order."""
+    on every rank, in image order.  Two host reads in all (block sizes, per-image counts); the
+    descriptor and keypoint exchanges are enqueued without one."""
     dev = local_desc.device
-    cnt = torch.as_tensor(np.asarray(local_counts, np.int64), device=dev)
-    descs = _all_gather_var(local_desc, group)
-    kps = _all_gather_var(local_kps, group)
-    cnts = _all_gather_var(cnt, group)
-    counts = torch.cat(cnts).cpu().numpy()
+    local_counts = np.asarray(local_counts, np.int64)
+    sizes = _gather_sizes([len(local_counts), local_desc.shape[0]], dev, group)       # [world, 2]
+    cnt = torch.as_tensor(local_counts, device=dev)
+    counts = _all_gather_rows(cnt, sizes[:, 0], group).cpu().numpy()
+    desc = _all_gather_rows(local_desc, sizes[:, 1], group)
+    kps = _all_gather_rows(local_kps, sizes[:, 1], group)
     off = np.zeros(len(counts) + 1, np.int64)
     off[1:] = np.cumsum(counts)
-    return torch.cat(descs).contiguous(), torch.cat(kps).contiguous(), off
+    return desc, kps, off
 
 
 def gather_to_root(t: torch.Tensor, group=None):
