@@ -302,9 +302,11 @@ SFM_API int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k
  * MMAs with the norm term folded into the contraction, unless a registered row has
  * ||b||^2 > 4,032,059, then the generic variant), 1 generic only, 5 wide folded kernel only,
  * 12 CTA-pair folded kernel (knn_pair.cu: cta_group::2, four accumulator stages), 15 wide kernel
- * with the warp-uniform skip of the unit bookkeeping (measured slower; kept for the A/B);
- * timing probes whose output is NOT a kNN: 6 / 13 max tree only (wide / pair), 7 / 14 TMA + MMA
- * pipeline without an epilogue. */
+ * with the warp-uniform skip of the unit bookkeeping (measured slower; kept for the A/B), 16 wide
+ * kernel with the lean unit tracker (fewer ALU instructions, same speed; A/B), 17 ping-pong kernel (the two accumulators alternate
+ * over train tiles of a 128-row query block; measured slower; kept for the A/B);
+ * timing probes whose output is NOT a kNN: 6 / 13 / 18 max tree only (wide / pair / ping-pong),
+ * 7 / 14 / 19 TMA + MMA pipeline without an epilogue. */
 SFM_API int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode);
 /* mbarrier suspend-time hints (ns; 0 = spin) of the kNN kernel's producer/MMA warps and of
  * its epilogue warps.  Tuning knob; results do not depend on it. */

@@ -105,6 +105,7 @@ struct sfm_ctx {
     CUtensorMap tmap_b64, tmap_x64;    // pair kNN variant: 64-row boxes of the descriptor / fold operand rows (knn_pair.cu)
     DevBuf<uint8_t> d_bias32;
     DevBuf<int32_t> d_fix_list;  // (work item, row) of the rows the wide kNN kernel leaves to its fix-up pass
+    DevBuf<int32_t> d_tie_list;  // ping-pong kNN kernel: rows with a dropped unit to merge in afterwards (8 ints each)
     static constexpr int32_t kFixCap = 1 << 18;
     bool have_tmap = false;
     DevBuf<int64_t> d_img_off, d_pad_off;
@@ -277,6 +278,7 @@ void sfm_destroy(sfm_ctx* ctx) {
     ctx->d_work_rev.release();
     ctx->d_par_bits.release();
     ctx->d_fix_list.release();
+    ctx->d_tie_list.release();
     ctx->d_pairs.release();
     ctx->d_meta.release();
     ctx->d_work.release();
@@ -410,14 +412,23 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     // knn_mode 0: the wide folded kernel (knn_wide.cu), or the generic one when a norm is beyond the fold range
     // (both are launched; the one that does not apply exits at its first instruction).  1: generic only,
     // 5: wide only, 6/7: its timing probes, 12: CTA-pair kernel (knn_pair.cu), 13/14: its timing probes,
-    // 15: wide with the warp-uniform skip of the unit bookkeeping.
+    // 15: wide with the warp-uniform skip of the unit bookkeeping, 16: wide with the lean tracker (A/B variants
+    // of the default tracker), 17: ping-pong kernel (accumulators alternate over train tiles), 18 / 19: its
+    // timing probes.
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
-    if (km == 15)   // wide kernel with the warp-uniform skip of the unit bookkeeping (A/B against mode 5)
+    if (km >= 15) {   // tracker variants of the wide kernel (A/B against mode 5), ping-pong kernel and its probes
+        int32_t tie_cap = 0;
+        if (km >= 17) {   // one entry per 8 query rows of the launch (1 % duplicated rows need about one per 25)
+            tie_cap = static_cast<int32_t>(std::min<int64_t>(n_work * (SFM_QBLOCK / 8) + 4096, int64_t(1) << 27));
+            SFM_CUDA(ctx, ctx->d_tie_list.reserve(8 * static_cast<size_t>(tie_cap)));
+        }
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
-                                  ctx->d_norms_pad.p, ctx->d_flags.p, 3, 1, ctx->knn_tuning, ctx->d_fix_list.p, fix_cap,
-                                  d_knn, ctx->num_sms, st, &ctx->launches);
+                                  ctx->d_norms_pad.p, ctx->d_flags.p, km - 12, ctx->knn_mode != 0, ctx->knn_tuning,
+                                  ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches, nullptr,
+                                  ctx->d_tie_list.p, tie_cap);
+    }
     else if (km >= 12)
         r = sfm::launch_knn2_pair(ctx->tmap, ctx->tmap_b64, ctx->tmap_x64, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p,
                                   n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
@@ -939,8 +950,8 @@ int sfm_debug_mma_handshake_probe(sfm_ctx* ctx, int32_t steps, int32_t k_per_acc
 
 int sfm_debug_set_knn_mode(sfm_ctx* ctx, int32_t mode) {
     if (!ctx) return 1;
-    if (!(mode == 0 || mode == 1 || (mode >= 5 && mode <= 7) || (mode >= 12 && mode <= 15)))
-        return ctx->fail("knn mode must be 0, 1, 5..7 or 12..15");
+    if (!(mode == 0 || mode == 1 || (mode >= 5 && mode <= 7) || (mode >= 12 && mode <= 19)))
+        return ctx->fail("knn mode must be 0, 1, 5..7 or 12..19");
     ctx->knn_mode = mode;
     return 0;
 }

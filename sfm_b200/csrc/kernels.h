@@ -57,7 +57,7 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
                      const int32_t* d_norms_pad,
                      int32_t* d_flags, int variant, int force, const struct KnnTuning& tn, int32_t* d_fix_list,
                      int32_t fix_cap, int32_t* d_knn, int num_sms, cudaStream_t st, int64_t* launches,
-                     const KnnQuery* query = nullptr);
+                     const KnnQuery* query = nullptr, int32_t* d_tie_list = nullptr, int32_t tie_cap = 0);
 int launch_debug_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                       int32_t q_row, int32_t t_row, int32_t* d_out, cudaStream_t st, int64_t* launches);
 

@@ -102,6 +102,7 @@ __global__ void tmem_ld_probe_kernel(int iters, int variant, long long* out) {
 //         bit 4: same A and B tile every time (else A differs per accumulator, B rotates)
 //         bit 5: consumer warps spin on a barrier that never completes (shared-memory polling load)
 //         bit 6: N = 256 (one accumulator of 256 columns per stage... two MMAs groups share A)
+//         bit 7: N = 160, one accumulator per step in a ring of THREE stages (480 TMEM columns)
 // blockDim = 32 * (1 + consumers); warp 0 issues.
 template <int N>
 __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, int flags) {
@@ -112,8 +113,8 @@ __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, 
     uint8_t* sa = base;              // 2 A tiles
     uint8_t* sb = base + 2 * kTile;  // 4 B tiles of 128 rows (2 of 256)
     uint64_t* full = reinterpret_cast<uint64_t*>(base + 6 * kTile);
-    uint64_t* empty = full + 2;
-    uint64_t* other = empty + 2;
+    uint64_t* empty = full + 3;
+    uint64_t* other = empty + 3;
     uint64_t* fin = other + 1;
     uint64_t* never = fin + 1;
     uint32_t* slot = reinterpret_cast<uint32_t*>(never + 1);
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, 
         reinterpret_cast<uint32_t*>(base)[i] = 0x01010101u * (i & 3);
     fence_proxy_async();
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 3; ++i) {
             mbar_init(&full[i], 1);
             mbar_init(&empty[i], consumers > 0 ? consumers : 1);
         }
@@ -141,18 +142,20 @@ __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, 
     tc_fence_after();
     const uint32_t tmem_base = *slot;
     constexpr uint32_t idesc = make_idesc_u8(128, N);
-    constexpr int kAcc = 256 / N;   // accumulators per stage
+    constexpr int kAcc = N == 160 ? 1 : 256 / N;   // accumulators per stage
+    constexpr int kStages = N == 160 ? 3 : 2;
+    constexpr int kStageCols = N == 160 ? 160 : 256;
     if (warp == 0) {
         uint32_t phase = 0;
         int stage = 0;
         for (int st = 0; st < steps; ++st) {
             if (flags & 2) mbar_wait(&empty[stage], phase ^ 1);
             if (!(flags & 8)) tc_fence_after();
-            const int bsel = (flags & 16) ? 0 : (N == 128 ? (st & 3) : (st & 1) * 2);
+            const int bsel = (flags & 16) ? 0 : (N == 128 ? (st & 3) : (st & 1) * 2);   // N = 160: 160 rows of a 256-row region
             const uint64_t bd = make_kmajor_sw128_desc(smem_u32(sb + bsel * kTile));
             const uint64_t ad0 = make_kmajor_sw128_desc(smem_u32(sa));
             const uint64_t astep = (flags & 16) ? 0 : (kTile >> 4);
-            const uint32_t d0 = tmem_base + stage * 256;
+            const uint32_t d0 = tmem_base + stage * kStageCols;
             if (elect_one()) {
 #pragma unroll
                 for (int a = 0; a < kAcc; ++a) {
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, 
                 if (flags & 1) mma_commit(&full[stage]);
             }
             __syncwarp();
-            if (++stage == 2) {
+            if (++stage == kStages) {
                 stage = 0;
                 phase ^= 1;
             }
@@ -183,7 +186,7 @@ __global__ void __launch_bounds__(320, 1) mma_handshake_probe_kernel(int steps, 
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
-            if (++stage == 2) {
+            if (++stage == kStages) {
                 stage = 0;
                 phase ^= 1;
             }
@@ -210,8 +213,13 @@ int launch_mma_handshake_probe(int steps, int k_per_acc, int flags, int consumer
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(mma_handshake_probe_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(smem));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(mma_handshake_probe_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(smem));
     if (e != cudaSuccess) return static_cast<int>(e);
-    if (flags & 64)
+    if (flags & 128)
+        mma_handshake_probe_kernel<160><<<num_sms, 32 * (1 + consumers), smem, st>>>(steps, flags);
+    else if (flags & 64)
         mma_handshake_probe_kernel<256><<<num_sms, 32 * (1 + consumers), smem, st>>>(steps, flags);
     else
         mma_handshake_probe_kernel<128><<<num_sms, 32 * (1 + consumers), smem, st>>>(steps, flags);

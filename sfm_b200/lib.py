@@ -457,7 +457,8 @@ class Context:
         return n.value / (ms.value * 1e-3)
 
     def set_knn_mode(self, mode: int):
-        """0 auto, 1 generic, 5 wide, 12 CTA pair, 15 wide + skip; 6 / 7 / 13 / 14 timing probes (sfm_match.h)."""
+        """0 auto, 1 generic, 5 wide, 12 CTA pair, 15 wide + skip, 16 wide + lean tracker, 17 ping-pong;
+        6 / 7 / 13 / 14 / 18 / 19 timing probes (sfm_match.h)."""
         self._check(self.lib.sfm_debug_set_knn_mode(self.h, mode))
 
     def set_knn_waits(self, wait_ns: int, epi_wait_ns: int):

@@ -40,7 +40,7 @@ for mode, (w_ns, e_ns), pf in [(m, w, f) for m in modes for w in waits for f in 
         torch.cuda.synchronize()
         ts.append(round(ops / (e0.elapsed_time(e1) * 1e-3) / 1e12, 1))
     out.setdefault(f"mode{mode}_w{w_ns}_e{e_ns}_pf{pf}_tops", []).append(ts)
-    if mode in (5, 12, 15) and pf == 0:
+    if mode in (5, 12, 15, 16, 17) and pf == 0:
         got = buf.clone()
         if ref is None:
             ref = got

@@ -18,7 +18,7 @@ s = synth.make_image_set(5, [300, 513, 40, 700, 129], seed=3, tie_frac=0.05)
 ctx = L.Context(0)
 ctx.set_images(s.desc.cuda(), s.kps.cuda(), s.offsets.numpy())
 pairs = np.array([(0, 1), (1, 3), (3, 0), (2, 4), (4, 1), (1, 0)], np.int32)
-for mode in (5, 12):
+for mode in (5, 12, 16, 17):
     ctx.set_knn_mode(mode)
     knn, ro = ctx.knn2(pairs)
     torch.cuda.synchronize()
@@ -30,7 +30,7 @@ ctx.set_knn_mode(0)
 base = s.image(0)[0][:5]
 ties = torch.cat([base[torch.randint(0, 5, (n,))] for n in (260, 300)])
 ctx.set_images(ties.cuda(), None, np.array([0, 260, 560], np.int64))
-for mode in (5, 12):
+for mode in (5, 12, 16, 17):
     ctx.set_knn_mode(mode)
     knn, ro = ctx.knn2([(0, 1), (1, 0)])
     rev, ro_rev = ctx.knn2([(1, 0), (0, 1)])

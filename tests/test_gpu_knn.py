@@ -253,7 +253,7 @@ def test_ts_fold_tile_accumulators(ctx):
         assert np.array_equal(got[:len(a), :len(b)], want)
 
 
-@pytest.mark.parametrize("mode", [5, 12, 15])
+@pytest.mark.parametrize("mode", [5, 12, 15, 16, 17])
 def test_knn_fixup_paths(ctx, mode):
     """Data made of few distinct descriptors: unit maxima tie everywhere, so the folded kernels'
     tied-unit recompute and their brute-force fix-up pass (list driven, and the overflow scan with the
@@ -277,7 +277,7 @@ def test_knn_fixup_paths(ctx, mode):
             check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-@pytest.mark.parametrize("mode", [5, 12, 15])
+@pytest.mark.parametrize("mode", [5, 12, 15, 16, 17])
 def test_knn_long_train_images(ctx, mode):
     """Folded kernels with long train images (wide: beyond 8192 rows, TS: beyond 16384): unit ids need
     more than 8 key bits, the unit maxima are truncated in the packed keys and ties on the truncated
@@ -295,7 +295,7 @@ def test_knn_long_train_images(ctx, mode):
         check_pair(got[ro[p]:ro[p + 1]], descs[i], descs[j])
 
 
-@pytest.mark.parametrize("mode", [1, 5, 12, 15])
+@pytest.mark.parametrize("mode", [1, 5, 12, 15, 16, 17])
 def test_knn_variants_match_oracle(ctx, mode):
     """Generic (1), N = 128 folded (2), wide folded (5) and TS (8) kernels, forced, on SIFT-like data
     with partial tiles and ties."""
