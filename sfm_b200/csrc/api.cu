@@ -904,7 +904,7 @@ int sfm_debug_ts_rate_probe(sfm_ctx* ctx, int32_t groups, int32_t tile_n, int32_
 int sfm_debug_tmem_ld_probe(sfm_ctx* ctx, int32_t warps, int32_t variant, int32_t iters, int64_t* h_cycles,
                             void* stream) {
     if (!ctx) return 1;
-    if (warps < 1 || warps > 16 || variant < 0 || variant > 3 || iters < 1 || !h_cycles)
+    if (warps < 1 || warps > 16 || variant < 0 || variant > 6 || iters < 1 || !h_cycles)
         return ctx->fail("bad probe arguments");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SFM_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -405,16 +405,14 @@ struct SmemLayout {
     }
 };
 
-// MODE 0: the kNN.  1: max tree only, 2: no epilogue (timing probes; output is not a kNN).
 template <int MODE, int TRK, bool PROF>
-__global__ void __launch_bounds__(kThreads, 1)
-knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap,
-                 const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_ax,
-                 const uint8_t* __restrict__ desc_q, const int32_t* __restrict__ norms_q,
-                 const uint8_t* __restrict__ desc,
-                 const WorkItem* __restrict__ work, long long n_work, const int32_t* __restrict__ norms_pad,
-                 int32_t* __restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns,
-                 uint32_t epi_wait_ns, int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out) {
+__device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const CUtensorMap& tmap, const CUtensorMap& tmap_x,
+                                               const CUtensorMap& tmap_ax, const uint8_t* __restrict__ desc_q,
+                                               const int32_t* __restrict__ norms_q, const uint8_t* __restrict__ desc,
+                                               const WorkItem* __restrict__ work, long long n_work,
+                                               const int32_t* __restrict__ norms_pad, int32_t* __restrict__ flags, int force,
+                                               uint32_t probe_flags, uint32_t wait_ns, uint32_t epi_wait_ns,
+                                               int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     constexpr bool kBatch = TRK == 0;   // dm / dd take two chunks per update
@@ -604,16 +602,18 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
                 tc_fence_after();
                 tphase ^= 1;
-                if (MODE == 2) {   // timing probe: TMA + MMA pipeline alone
+                // MODE 2: timing probe, TMA + MMA pipeline alone.  Probe bit 8: the second row block's warps hand
+                // their accumulator back at once, so the first one's eight warps have the SM to themselves.
+                if (MODE == 2 || (PROF && (probe_flags & 256u) && acc == 1)) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(empty);
                     continue;
                 }
+                const uint32_t ut = static_cast<uint32_t>(kf.n_units - 1 - t * (kColsPerThread / kUnit)) << 1;
                 // 16-column chunks, double-buffered: 32 live accumulator registers per thread
                 uint32_t v[2][16];
                 tmem_ld_32x16(taddr, v[0]);
-                const uint32_t ut = static_cast<uint32_t>(kf.n_units - 1 - t * (kColsPerThread / kUnit)) << 1;
                 if ((t + 1) * kTileN <= t_cnt && kf.sh == 0) {
 #pragma unroll
                     for (int c = 0; c < kColsPerThread / 16; ++c) {
@@ -663,7 +663,7 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
             }
             const long long pe0 = prof ? clock64() : 0;
-            if (MODE != 0) {
+            if (MODE != 0 || (PROF && (probe_flags & 256u) && acc == 1)) {
                 if (valid && half == 0) out[out_row + row] = make_int4(static_cast<int>(sk.k1), static_cast<int>(sk.k2), na, 0);   // keeps the probe live
                 continue;
             }
@@ -739,6 +739,24 @@ knn2_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tmem_dealloc(tmem_base, kTmemCols);
     }
 }
+
+// MODE 0: the kNN.  1: max tree only, 2: no epilogue (timing probes; output is not a kNN).
+#define SFM_WIDE_PARAMS                                                                                                  \
+    const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap,                                \
+        const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_ax,                         \
+        const uint8_t *__restrict__ desc_q, const int32_t *__restrict__ norms_q, const uint8_t *__restrict__ desc,       \
+        const WorkItem *__restrict__ work, long long n_work, const int32_t *__restrict__ norms_pad,                      \
+        int32_t *__restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns, uint32_t epi_wait_ns,            \
+        int2 *__restrict__ fix_list, int fix_cap, int4 *__restrict__ out
+#define SFM_WIDE_FWD                                                                                                     \
+    tmap_q, tmap, tmap_x, tmap_ax, desc_q, norms_q, desc, work, n_work, norms_pad, flags, force, probe_flags, wait_ns,   \
+        epi_wait_ns, fix_list, fix_cap, out
+template <int MODE, int TRK, bool PROF>
+__global__ void __launch_bounds__(kThreads, 1) knn2_wide_kernel(SFM_WIDE_PARAMS) {
+    knn2_wide_body<MODE, TRK, PROF>(SFM_WIDE_FWD);
+}
+#undef SFM_WIDE_PARAMS
+#undef SFM_WIDE_FWD
 
 // (key desc, index asc) merge of two per-thread top-2 results of one row; empty entries carry index INT_MAX.
 __device__ __forceinline__ Top2K merge_top2(const Top2K& r, const Top2K& b) {
@@ -1393,17 +1411,16 @@ cudaError_t launch_variant(const KnnQuery& q, const CUtensorMap& tmap, const CUt
                            const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work,
                            const int32_t* d_norms_pad, int32_t* d_flags, int force, const KnnTuning& tn,
                            int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid, cudaStream_t st) {
+    auto kern = knn2_wide_kernel<MODE, TRK, PROF>;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(knn2_wide_kernel<MODE, TRK, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             static_cast<int>(kSmemBytes));
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemBytes));
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    knn2_wide_kernel<MODE, TRK, PROF><<<grid, kThreads, kSmemBytes, st>>>(*q.tmap, tmap, tmap_x, tmap_ax, q.desc, q.norms, d_desc,
-                                                              d_work, n_work,
-                                                              d_norms_pad, d_flags, force, tn.probe_flags, tn.wait_ns,
-                                                              tn.epi_wait_ns, d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
+    kern<<<grid, kThreads, kSmemBytes, st>>>(*q.tmap, tmap, tmap_x, tmap_ax, q.desc, q.norms, d_desc, d_work, n_work,
+                                             d_norms_pad, d_flags, force, tn.probe_flags, tn.wait_ns, tn.epi_wait_ns,
+                                             d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
 }
 
@@ -1453,7 +1470,7 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
     cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, 2 * sizeof(int32_t), st);   // lengths of this launch's fix and tie lists
     if (e != cudaSuccess) return static_cast<int>(e);
 #define SFM_WIDE_ARGS q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags
-    const bool prof = (tn.probe_flags & (16u | 32u | 64u)) != 0;   // cycle counters / probe switches compiled in
+    const bool prof = (tn.probe_flags & (16u | 32u | 64u | 256u)) != 0;   // cycle counters / probe switches compiled in
     if (variant == 1)
         e = prof ? launch_variant<1, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st)
                  : launch_variant<1, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st);

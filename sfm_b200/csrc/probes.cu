@@ -51,6 +51,7 @@ __device__ __forceinline__ void tmem_ld_16x256_x8(uint32_t taddr) {
 //         1: 32x32b.x32, wait after every 4 loads
 //         2: 32x32b.x64, wait after each load         (8 KiB)
 //         3: 16x256b.x8, wait after every 4 loads     (4 KiB... 16 lanes x 64 columns)
+//         4 / 5 / 6: 32x32b.x16 (2 KiB), wait after each / every second / every eighth load
 __global__ void tmem_ld_probe_kernel(int iters, int variant, long long* out) {
     __shared__ uint32_t slot;
     const int warp = threadIdx.x >> 5;
@@ -75,9 +76,21 @@ __global__ void tmem_ld_probe_kernel(int iters, int variant, long long* out) {
         } else if (variant == 2) {
             tmem_ld_x64(base + (col & 448));
             tmem_ld_wait();
-        } else {
+        } else if (variant == 3) {
             tmem_ld_16x256_x8(base + (col & 448));
             if ((i & 3) == 3) tmem_ld_wait();
+        } else if (variant == 4) {   // the kNN epilogue's own shape: 32x32b.x16, wait after each
+            uint32_t v[16];
+            tmem_ld_32x16(base + (col & 496), v);
+            tmem_ld_wait();
+        } else if (variant == 5) {   // ... wait after every second load
+            uint32_t v[16];
+            tmem_ld_32x16(base + (col & 496), v);
+            if (i & 1) tmem_ld_wait();
+        } else {                     // ... wait after every eighth load
+            uint32_t v[16];
+            tmem_ld_32x16(base + (col & 496), v);
+            if ((i & 7) == 7) tmem_ld_wait();
         }
     }
     tmem_ld_wait();

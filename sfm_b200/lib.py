@@ -447,7 +447,7 @@ class Context:
         """-> bytes of TMEM read per cycle per SM for the given warp count / load shape."""
         cyc = C.c_int64(0)
         self._check(self.lib.sfm_debug_tmem_ld_probe(self.h, warps, variant, iters, C.byref(cyc), self._stream()))
-        per = {0: 4096, 1: 4096, 2: 8192, 3: 4096}[variant]
+        per = {0: 4096, 1: 4096, 2: 8192, 3: 4096, 4: 2048, 5: 2048, 6: 2048}[variant]
         return per * iters * warps / cyc.value, cyc.value
 
     def probe_fp64_rate(self, iters=4096):

@@ -18,9 +18,10 @@ pairs = np.array([(i, j) for i in range(n_img) for j in range(i + 1, n_img)], np
 ro = ctx.query_rows(pairs)
 buf = ctx.empty((int(ro[-1]), 4), torch.int32)
 out = {}
+pf_extra = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 for mode in [int(m) for m in (sys.argv[1].split(",") if len(sys.argv) > 1 else "5,6,7,17,18,19".split(","))]:
     ctx.set_knn_mode(mode)
-    ctx.set_knn_probe_flags(16)
+    ctx.set_knn_probe_flags(16 | pf_extra)
     ctx.knn2(pairs, ro, buf)
     torch.cuda.synchronize()
     c = ctx.pair_counters()
@@ -36,4 +37,4 @@ for mode in [int(m) for m in (sys.argv[1].split(",") if len(sys.argv) > 1 else "
 ctx.set_knn_mode(0)
 ctx.set_knn_probe_flags(0)
 Path("gpurun_out").mkdir(exist_ok=True)
-Path("gpurun_out/r02_probe_wide_counters.json").write_text(json.dumps(out, indent=1))
+Path(f"gpurun_out/r02_probe_wide_counters_pf{pf_extra}.json").write_text(json.dumps(out, indent=1))
