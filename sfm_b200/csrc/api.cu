@@ -418,17 +418,18 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     const int km = ctx->knn_mode == 0 ? ctx->knn_auto : ctx->knn_mode;
     int r = 0;
     const int32_t fix_cap = (ctx->knn_tuning.probe_flags & 8u) ? 4 : sfm_ctx::kFixCap;
-    if (km >= 15) {   // tracker variants of the wide kernel (A/B against mode 5), ping-pong kernel and its probes
-        int32_t tie_cap = 0;
-        if (km >= 17) {   // one entry per 8 query rows of the launch (1 % duplicated rows need about one per 25)
-            tie_cap = static_cast<int32_t>(std::min<int64_t>(n_work * (SFM_QBLOCK / 8) + 4096, int64_t(1) << 27));
-            SFM_CUDA(ctx, ctx->d_tie_list.reserve(8 * static_cast<size_t>(tie_cap)));
-        }
+    // tie list of the wide and ping-pong kernels (rows with a dropped unit to merge in afterwards): one entry per 8
+    // query rows of the launch (1 % duplicated rows need about one per 25); a full list sends rows to the fix-up pass
+    int32_t tie_cap = 0;
+    if (km >= 5 && !(km >= 12 && km <= 14)) {
+        tie_cap = static_cast<int32_t>(std::min<int64_t>(n_work * (SFM_QBLOCK / 8) + 4096, int64_t(1) << 27));
+        SFM_CUDA(ctx, ctx->d_tie_list.reserve(8 * static_cast<size_t>(tie_cap)));
+    }
+    if (km >= 15)   // tracker variants of the wide kernel (A/B against mode 5), ping-pong kernel and its probes
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km - 12, ctx->knn_mode != 0, ctx->knn_tuning,
                                   ctx->d_fix_list.p, fix_cap, d_knn, ctx->num_sms, st, &ctx->launches, nullptr,
                                   ctx->d_tie_list.p, tie_cap);
-    }
     else if (km >= 12)
         r = sfm::launch_knn2_pair(ctx->tmap, ctx->tmap_b64, ctx->tmap_x64, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p,
                                   n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_par_bits.p, ctx->d_flags.p,
@@ -438,7 +439,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
         r = sfm::launch_knn2_wide(ctx->tmap, ctx->tmap_x32, ctx->tmap_ax32, ctx->d_desc, ctx->d_work.p, n_work, ctx->d_norms.p,
                                   ctx->d_norms_pad.p, ctx->d_flags.p, km >= 6 ? km - 5 : 0, ctx->knn_mode != 0,
                                   ctx->knn_tuning, ctx->d_fix_list.p, fix_cap, d_knn,
-                                  ctx->num_sms, st, &ctx->launches);
+                                  ctx->num_sms, st, &ctx->launches, nullptr, ctx->d_tie_list.p, tie_cap);
     const bool folded_auto = (km == 5 || km == 12) && ctx->knn_mode == 0;
     if (!r && (km == 1 || folded_auto))
         r = sfm::launch_knn2(ctx->tmap, ctx->d_work.p, n_work, ctx->d_norms.p, ctx->d_norms_pad.p, ctx->d_flags.p,

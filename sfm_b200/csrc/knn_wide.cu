@@ -160,6 +160,25 @@ __device__ __forceinline__ void top2k_insert_ordered(Top2K& s, int key, int col)
     }
 }
 
+// (key desc, index asc) merge of two per-thread top-2 results of one row; empty entries carry index INT_MAX.
+__device__ __forceinline__ Top2K merge_top2(const Top2K& r, const Top2K& b) {
+    Top2K mrg;
+    if (key_before(r.k1, r.i1, b.k1, b.i1)) {
+        mrg.k1 = r.k1;
+        mrg.i1 = r.i1;
+        const bool mine = key_before(r.k2, r.i2, b.k1, b.i1);
+        mrg.k2 = mine ? r.k2 : b.k1;
+        mrg.i2 = mine ? r.i2 : b.i1;
+    } else {
+        mrg.k1 = b.k1;
+        mrg.i1 = b.i1;
+        const bool theirs = key_before(b.k2, b.i2, r.k1, r.i1);
+        mrg.k2 = theirs ? b.k2 : r.k1;
+        mrg.i2 = theirs ? b.i2 : r.i1;
+    }
+    return mrg;
+}
+
 // 16 folded accumulators of one row = one unit, chunk c of its tile; ut = uidrev << 1 of chunk 0.
 // MASKED: columns >= t_cnt (last, partial train tile) count as v = 0 (real accumulators are >= 0;
 // resolve_units skips them by column).  TREE_ONLY: timing probe.
@@ -412,7 +431,8 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
                                                const WorkItem* __restrict__ work, long long n_work,
                                                const int32_t* __restrict__ norms_pad, int32_t* __restrict__ flags, int force,
                                                uint32_t probe_flags, uint32_t wait_ns, uint32_t epi_wait_ns,
-                                               int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ out) {
+                                               int2* __restrict__ fix_list, int fix_cap, int4* __restrict__ tie_list,
+                                               int tie_cap, int4* __restrict__ out) {
     constexpr int kProducerWarp = kEpiWarps;
     constexpr int kMmaWarp = kEpiWarps + 1;
     constexpr bool kBatch = TRK == 0;   // dm / dd take two chunks per update
@@ -673,8 +693,14 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
             // a dropped unit whose (truncated) maximum equals the second kept one may hold a candidate:
             // the best dropped one is recomputed here, a second one sends the row to knn_fix_kernel
             const uint32_t mf = kf.ubits + 1;
-            r = recompute_units(r, valid && n_in >= 3 && (sk.dm >> mf) == (sk.k2 >> mf), q_row + row,
-                                key_col(sk.dm, kf, colbase), desc_q, desc, t_row, t_cnt, nbase);
+            // With a tie list the unit is not recomputed here: the row goes out as it is and (row, unit) is appended
+            // for knn_tie_kernel, which merges the unit's 16 keys into the row afterwards (see knn2_pp_kernel).
+            const bool need = valid && n_in >= 3 && (sk.dm >> mf) == (sk.k2 >> mf);
+            int ncol = -1;
+            if (tie_list)
+                ncol = need ? key_col(sk.dm, kf, colbase) : -1;
+            else
+                r = recompute_units(r, need, q_row + row, key_col(sk.dm, kf, colbase), desc_q, desc, t_row, t_cnt, nbase);
             const bool tie = n_in >= 4 && (sk.dd >> mf) == (sk.k2 >> mf);
             // the thread of the upper column half hands its top-2 to the lower half's thread,
             // which merges under the (key, lowest index) order and writes the row
@@ -682,30 +708,30 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
             const uint32_t faddr = smem_u32(sm.pub) + ((item & 1) * SFM_QBLOCK + row) * 4;
             if (half == 1) {
                 sts128(xaddr, r.k1, r.k2, r.i1, r.i2);
-                sts32(faddr, tie ? 1u : 0u);
+                sts32(faddr, (static_cast<uint32_t>(ncol + 1) << 1) | (tie ? 1u : 0u));
             }
             asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp & 7)) : "memory");
             if (half == 0) {
                 const uint4 o = lds128(xaddr);
-                const bool flagged = tie || lds32(faddr) != 0;
+                const uint32_t pw = lds32(faddr);
+                bool flagged = tie || (pw & 1u) != 0;
+                const int ncol_b = static_cast<int>(pw >> 1) - 1;
                 Top2K b{static_cast<int>(o.x), static_cast<int>(o.y), static_cast<int>(o.z), static_cast<int>(o.w)};
                 if (b.i1 < 0) b.i1 = INT_MAX;   // empty entries sort last
                 if (b.i2 < 0) b.i2 = INT_MAX;
                 if (r.i1 < 0) r.i1 = INT_MAX;
                 if (r.i2 < 0) r.i2 = INT_MAX;
-                Top2K mrg;
-                if (key_before(r.k1, r.i1, b.k1, b.i1)) {
-                    mrg.k1 = r.k1;
-                    mrg.i1 = r.i1;
-                    const bool mine = key_before(r.k2, r.i2, b.k1, b.i1);
-                    mrg.k2 = mine ? r.k2 : b.k1;
-                    mrg.i2 = mine ? r.i2 : b.i1;
-                } else {
-                    mrg.k1 = b.k1;
-                    mrg.i1 = b.i1;
-                    const bool theirs = key_before(b.k2, b.i2, r.k1, r.i1);
-                    mrg.k2 = theirs ? b.k2 : r.k1;
-                    mrg.i2 = theirs ? b.i2 : r.i1;
+                const Top2K mrg = merge_top2(r, b);
+                if (valid && !flagged && (ncol & ncol_b) >= 0) {   // some unit to patch in
+                    const int e = atomicAdd(flags + 3, 1);
+                    if (e < tie_cap) {
+                        const long long o_idx = out_row + row;
+                        tie_list[2 * e] = make_int4(static_cast<int>(static_cast<uint32_t>(o_idx)),
+                                                    static_cast<int>(o_idx >> 32), q_row + row, static_cast<int>(w));
+                        tie_list[2 * e + 1] = make_int4(ncol, ncol_b, -1, -1);
+                    } else {
+                        flagged = true;   // list full: brute force instead
+                    }
                 }
                 if (valid && flagged) {   // rare: left to knn_fix_kernel
                     atomicAdd(flags + 1, 1);   // statistics since sfm_set_images
@@ -747,35 +773,16 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
         const uint8_t *__restrict__ desc_q, const int32_t *__restrict__ norms_q, const uint8_t *__restrict__ desc,       \
         const WorkItem *__restrict__ work, long long n_work, const int32_t *__restrict__ norms_pad,                      \
         int32_t *__restrict__ flags, int force, uint32_t probe_flags, uint32_t wait_ns, uint32_t epi_wait_ns,            \
-        int2 *__restrict__ fix_list, int fix_cap, int4 *__restrict__ out
+        int2 *__restrict__ fix_list, int fix_cap, int4 *__restrict__ tie_list, int tie_cap, int4 *__restrict__ out
 #define SFM_WIDE_FWD                                                                                                     \
     tmap_q, tmap, tmap_x, tmap_ax, desc_q, norms_q, desc, work, n_work, norms_pad, flags, force, probe_flags, wait_ns,   \
-        epi_wait_ns, fix_list, fix_cap, out
+        epi_wait_ns, fix_list, fix_cap, tie_list, tie_cap, out
 template <int MODE, int TRK, bool PROF>
 __global__ void __launch_bounds__(kThreads, 1) knn2_wide_kernel(SFM_WIDE_PARAMS) {
     knn2_wide_body<MODE, TRK, PROF>(SFM_WIDE_FWD);
 }
 #undef SFM_WIDE_PARAMS
 #undef SFM_WIDE_FWD
-
-// (key desc, index asc) merge of two per-thread top-2 results of one row; empty entries carry index INT_MAX.
-__device__ __forceinline__ Top2K merge_top2(const Top2K& r, const Top2K& b) {
-    Top2K mrg;
-    if (key_before(r.k1, r.i1, b.k1, b.i1)) {
-        mrg.k1 = r.k1;
-        mrg.i1 = r.i1;
-        const bool mine = key_before(r.k2, r.i2, b.k1, b.i1);
-        mrg.k2 = mine ? r.k2 : b.k1;
-        mrg.i2 = mine ? r.i2 : b.i1;
-    } else {
-        mrg.k1 = b.k1;
-        mrg.i1 = b.i1;
-        const bool theirs = key_before(b.k2, b.i2, r.k1, r.i1);
-        mrg.k2 = theirs ? b.k2 : r.k1;
-        mrg.i2 = theirs ? b.i2 : r.i1;
-    }
-    return mrg;
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // Ping-pong variant (knn mode 17).  Cycle counters of the wide kernel (probe bit 4, profiles/
@@ -1410,7 +1417,8 @@ template <int MODE, int TRK, bool PROF = false>
 cudaError_t launch_variant(const KnnQuery& q, const CUtensorMap& tmap, const CUtensorMap& tmap_x, const CUtensorMap& tmap_ax,
                            const uint8_t* d_desc, const WorkItem* d_work, int64_t n_work,
                            const int32_t* d_norms_pad, int32_t* d_flags, int force, const KnnTuning& tn,
-                           int2* d_fix_list, int fix_cap, int32_t* d_knn, unsigned grid, cudaStream_t st) {
+                           int2* d_fix_list, int fix_cap, int4* d_tie_list, int tie_cap, int32_t* d_knn, unsigned grid,
+                           cudaStream_t st) {
     auto kern = knn2_wide_kernel<MODE, TRK, PROF>;
     static bool configured = false;
     if (!configured) {
@@ -1420,7 +1428,7 @@ cudaError_t launch_variant(const KnnQuery& q, const CUtensorMap& tmap, const CUt
     }
     kern<<<grid, kThreads, kSmemBytes, st>>>(*q.tmap, tmap, tmap_x, tmap_ax, q.desc, q.norms, d_desc, d_work, n_work,
                                              d_norms_pad, d_flags, force, tn.probe_flags, tn.wait_ns, tn.epi_wait_ns,
-                                             d_fix_list, fix_cap, reinterpret_cast<int4*>(d_knn));
+                                             d_fix_list, fix_cap, d_tie_list, tie_cap, reinterpret_cast<int4*>(d_knn));
     return cudaGetLastError();
 }
 
@@ -1472,15 +1480,15 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
 #define SFM_WIDE_ARGS q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags
     const bool prof = (tn.probe_flags & (16u | 32u | 64u | 256u)) != 0;   // cycle counters / probe switches compiled in
     if (variant == 1)
-        e = prof ? launch_variant<1, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st)
-                 : launch_variant<1, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st);
+        e = prof ? launch_variant<1, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
+                 : launch_variant<1, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
     else if (variant == 2)
-        e = prof ? launch_variant<2, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st)
-                 : launch_variant<2, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, d_knn, grid, st);
+        e = prof ? launch_variant<2, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
+                 : launch_variant<2, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
     else if (variant == 3)   // the kNN WITH the warp-uniform skip of the unit bookkeeping (A/B: 5 % slower)
-        e = launch_variant<0, 1>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, d_knn, grid, st);
+        e = launch_variant<0, 1>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
     else if (variant == 4)   // lean tracker (A/B: 7 % fewer ALU-pipe instructions, same speed)
-        e = launch_variant<0, 0>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, d_knn, grid, st);
+        e = launch_variant<0, 0>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
     else if (variant == 5)   // ping-pong kernel
         e = prof ? launch_pp<0, 0, true>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
                  : launch_pp<0, 0>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
@@ -1491,11 +1499,11 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
         e = prof ? launch_pp<2, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
                  : launch_pp<2, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
     else
-        e = prof ? launch_variant<0, 2, true>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, d_knn, grid, st)
-                 : launch_variant<0, 2>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, d_knn, grid, st);
+        e = prof ? launch_variant<0, 2, true>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
+                 : launch_variant<0, 2>(SFM_WIDE_ARGS, force, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
 #undef SFM_WIDE_ARGS
     ++*launches;
-    if (e == cudaSuccess && variant == 5 && tl && !(tn.probe_flags & 4u)) {
+    if (e == cudaSuccess && (variant == 0 || (variant >= 3 && variant <= 5)) && tl && !(tn.probe_flags & 4u)) {
         knn_tie_kernel<<<4 * num_sms, 256, 0, st>>>(d_work, q.desc, q.norms, d_desc, d_norms, d_flags, tl, tie_cap,
                                                     reinterpret_cast<int4*>(d_knn));
         ++*launches;
