@@ -423,6 +423,7 @@ int sfm_knn2(sfm_ctx* ctx, const int32_t* h_pairs, int32_t n_pairs, const int64_
     int32_t tie_cap = 0;
     if (km >= 5 && !(km >= 12 && km <= 14)) {
         tie_cap = static_cast<int32_t>(std::min<int64_t>(n_work * (SFM_QBLOCK / 8) + 4096, int64_t(1) << 27));
+        if (ctx->knn_tuning.probe_flags & 512u) tie_cap = 2;   // test switch: the overflow path (rows go to the fix-up pass)
         SFM_CUDA(ctx, ctx->d_tie_list.reserve(8 * static_cast<size_t>(tie_cap)));
     }
     if (km >= 15)   // tracker variants of the wide kernel (A/B against mode 5), ping-pong kernel and its probes

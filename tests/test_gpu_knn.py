@@ -256,14 +256,16 @@ def test_ts_fold_tile_accumulators(ctx):
 @pytest.mark.parametrize("mode", [5, 12, 15, 16, 17])
 def test_knn_fixup_paths(ctx, mode):
     """Data made of few distinct descriptors: unit maxima tie everywhere, so the folded kernels'
-    tied-unit recompute and their brute-force fix-up pass (list driven, and the overflow scan with the
-    list shrunk to 4 entries) produce the rows; all must equal the oracle incl. the tie rule."""
+    tied-unit recompute (in the kernel or through the tie list, also with the list overflowing) and their
+    brute-force fix-up pass (list driven, and the overflow scan with the list shrunk to 4 entries) produce
+    the rows; all must equal the oracle incl. the tie rule."""
     rng = np.random.default_rng(77)
     base = _sift_like([6], 41)[0]
     descs = [base[rng.integers(0, 6, n)] for n in (300, 1100, 520)]
     register(ctx, descs)
     pairs = [(0, 1), (1, 2), (2, 0), (1, 0)]
-    for pf in (0, 8):
+    # 128: tied units recomputed in the kernel, 512: tie list of 2 entries (wide and ping-pong kernels only)
+    for pf in ((0, 8) if mode == 12 else (0, 8, 128, 512, 512 | 8)):
         ctx.set_knn_mode(mode)
         ctx.set_knn_probe_flags(pf)
         try:
