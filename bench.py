@@ -573,7 +573,7 @@ def run_b200(args):
                          "frac": k_tops / peak, "frac_of_nominal_4500": k_tops / NOMINAL_INT8_TOPS,
                          "traffic": traffic,
                          "kernel": "knn2_wide_kernel (TMA + tcgen05 kind::i8 128x256x32, two accumulators in TMEM, "
-                                   "norm-fold K step, fused top-2 epilogue) + its fix-up pass",
+                                   "norm-fold K step, fused top-2 epilogue) + its tie-list and fix-up passes",
                          "kernel_ms": k_ms, "kernel_pairs": int(len(kp)),
                          "algorithmic_ops_per_launch": k_ops,
                          "peak_source": ("measured: MMA-only tcgen05 kind::i8 loop on every SM, profiles/int8_peak.json "
