@@ -545,13 +545,14 @@ def run_b200(args):
             int8_peak = json.loads((ROOT / "profiles" / "int8_peak.json").read_text())
         except Exception:
             pass
-        traffic = None
+        traffic = traffic_of = None
         tp = ROOT / "profiles" / "knn2_traffic.json"
         if tp.exists():
             try:
-                traffic = json.loads(tp.read_text()).get("dram_bytes_per_launch")
+                tj = json.loads(tp.read_text())
+                traffic, traffic_of = tj.get("dram_bytes_per_launch"), tj.get("workload")
             except Exception:
-                traffic = None
+                traffic = traffic_of = None
         peak = float(int8_peak["int8_tops_measured"]) if int8_peak else NOMINAL_INT8_TOPS
         whole_tops = cmp_s * OPS_PER_CMP / 1e12
         ransac_ms = st_local.get("ransac", 0.0)
@@ -571,7 +572,7 @@ def run_b200(args):
             "stages_ms": stages,
             "roofline": {"bound": "tensor", "achieved": k_tops, "peak": peak, "unit": "TOP/s",
                          "frac": k_tops / peak, "frac_of_nominal_4500": k_tops / NOMINAL_INT8_TOPS,
-                         "traffic": traffic,
+                         "traffic": traffic, "traffic_launch": traffic_of,   # the ncu capture's own launch shape
                          "kernel": "knn2_wide_kernel (TMA + tcgen05 kind::i8 128x256x32, two accumulators in TMEM, "
                                    "norm-fold K step, fused top-2 epilogue) + its tie-list and fix-up passes",
                          "kernel_ms": k_ms, "kernel_pairs": int(len(kp)),
