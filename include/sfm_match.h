@@ -315,11 +315,12 @@ SFM_API int sfm_debug_set_knn_waits(sfm_ctx* ctx, int32_t wait_ns, int32_t epi_w
  * producer skips the train-tile TMA loads (generic and pair kernels), bit 1 the MMA warp skips the tcgen05.mma
  * issue, bit 2 the wide kernel runs without its tie-list and fix-up passes, bit 5 without its parking
  * stores, bit 6 (ping-pong kernel) without the end-of-pass work, bit 8 the second row block's epilogue
- * warps of the wide kernel do no work.  Bit 4: CTA 0 of the wide / ping-pong kernel counts cycles in
+ * warps of the wide kernel do no work, bit 10 the wide kernel issues only the first of a tile's eight
+ * TMEM loads per thread.  Bit 4: CTA 0 of the wide / ping-pong kernel counts cycles in
  * its MMA warp and its first epilogue warp; sfm_debug_pair_counters reads them: [0] epilogue loop,
  * [1] of it waiting for a full accumulator, [2] for tcgen05.ld, [3] at the end of work items, [4] MMA
  * warp's loop, [5] of it waiting for train tiles, [6] for an empty accumulator, [7] tiles counted.
- * (Bits 4, 5, 6, 8 select a separate instantiation of the kernel: compiled into the default one the
+ * (Bits 4, 5, 6, 8, 10 select a separate instantiation of the kernel: compiled into the default one the
  * counters cost 15 %.)  Test switches (results stay exact): bit 3 shrinks the fix-up list to 4
  * entries, so its overflow scan is exercised; bit 7 makes the wide and ping-pong kernels recompute
  * tied units inside the kernel instead of deferring them to the tie list; bit 9 shrinks the tie list

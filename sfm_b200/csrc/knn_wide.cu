@@ -635,13 +635,16 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
                 uint32_t v[2][16];
                 tmem_ld_32x16(taddr, v[0]);
                 if ((t + 1) * kTileN <= t_cnt && kf.sh == 0) {
+                    // probe bit 10: only the first of a tile's eight TMEM loads is issued (the other chunks reuse
+                    // whatever the registers hold): the epilogue's own dependency chains without the loads
+                    const bool no_ld = PROF && (probe_flags & 1024u);
 #pragma unroll
                     for (int c = 0; c < kColsPerThread / 16; ++c) {
                         p0 = prof ? clock64() : 0;
-                        tmem_ld_wait();
+                        if (!no_ld || c == 0) tmem_ld_wait();
                         if (prof) pc_l += clock64() - p0;
                         if (c + 1 < kColsPerThread / 16) {
-                            tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
+                            if (!no_ld) tmem_ld_32x16(taddr + (c + 1) * 16, v[(c + 1) & 1]);
                         } else {
                             // every column of this thread is in registers: hand the accumulator back
                             tc_fence_before();
@@ -683,7 +686,7 @@ __device__ __forceinline__ void knn2_wide_body(const CUtensorMap& tmap_q, const 
                 }
             }
             const long long pe0 = prof ? clock64() : 0;
-            if (MODE != 0 || (PROF && (probe_flags & 256u) && acc == 1)) {
+            if (MODE != 0 || (PROF && (((probe_flags & 256u) && acc == 1) || (probe_flags & 1024u)))) {
                 if (valid && half == 0) out[out_row + row] = make_int4(static_cast<int>(sk.k1), static_cast<int>(sk.k2), na, 0);   // keeps the probe live
                 continue;
             }
@@ -1478,7 +1481,7 @@ int launch_knn2_wide(const CUtensorMap& tmap, const CUtensorMap& tmap_x, const C
     cudaError_t e = cudaMemsetAsync(d_flags + 2, 0, 2 * sizeof(int32_t), st);   // lengths of this launch's fix and tie lists
     if (e != cudaSuccess) return static_cast<int>(e);
 #define SFM_WIDE_ARGS q, tmap, tmap_x, tmap_ax, d_desc, d_work, n_work, d_norms_pad, d_flags
-    const bool prof = (tn.probe_flags & (16u | 32u | 64u | 256u)) != 0;   // cycle counters / probe switches compiled in
+    const bool prof = (tn.probe_flags & (16u | 32u | 64u | 256u | 1024u)) != 0;   // cycle counters / probe switches compiled in
     if (variant == 1)
         e = prof ? launch_variant<1, 0, true>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st)
                  : launch_variant<1, 0>(SFM_WIDE_ARGS, 1, tn, fl, fix_cap, tl, tie_cap, d_knn, grid, st);
