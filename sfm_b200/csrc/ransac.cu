@@ -50,6 +50,7 @@ struct Shared {
     float best_cost;
     int need;
     int flag;
+    float np_res[6];   // NumPy-exact float32 gate quantities of a borderline pair: std x1, y1, x2, y2, mean inlier error, mean error
 };
 
 template <int N>
@@ -73,6 +74,125 @@ __device__ void block_sum(double (&v)[N], Shared& sh) {
 #pragma unroll
     for (int i = 0; i < N; ++i) v[i] = sh.res[i];
     __syncthreads();
+}
+
+// ---- the reference's NumPy float32 arithmetic, restated instruction for instruction -------------------------
+// verify_match_quality's gates read np.std(pts[inlier_mask], axis=0) and np.mean(symmetric_errors[inlier_mask])
+// (utils/find_matches.py:176-186): float32 arrays, so NumPy sums in float32 -- SEQUENTIALLY along axis 0 of the
+// (I, 2) point arrays (the reduction axis is the outer one) and PAIRWISE along the contiguous 1-D error array
+// (eight accumulators per block of <= 128, halves split at multiples of 8).  A pair whose spread or error sits
+// within float32 rounding of a gate would otherwise flip against the reference.  One thread per quantity walks the
+// pair's matches in order; no FMA contraction (__f*_rn).
+// np.std of coordinate `k` (0..3 = x1, y1, x2, y2) over the inliers.
+// np.std of two coordinates (src[stride * i], src[stride * i + 1] of match i) over the inliers; err[i] is the
+// match's symmetric error (inlier <=> err[i] < thr, the comparison that made the mask).  Two independent chains per
+// loop.  Shared or global memory (generic pointers).
+__device__ __noinline__ float2 np_std2_f32(const float* src, int stride, const float* err, float thr, int m, int n_in) {
+    // (loads outside the condition: they are independent of the running sums and pipeline)
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll 8
+    for (int i = 0; i < m; ++i) {
+        const float e = err[i], x0 = src[stride * i], x1 = src[stride * i + 1];
+        if (e < thr) {
+            s0 = __fadd_rn(s0, x0);
+            s1 = __fadd_rn(s1, x1);
+        }
+    }
+    const float fn = static_cast<float>(n_in);
+    const float m0 = __fdiv_rn(s0, fn), m1 = __fdiv_rn(s1, fn);
+    float q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+    for (int i = 0; i < m; ++i) {
+        const float e = err[i];
+        const float d0 = __fsub_rn(src[stride * i], m0), d1 = __fsub_rn(src[stride * i + 1], m1);
+        const float p0 = __fmul_rn(d0, d0), p1 = __fmul_rn(d1, d1);
+        if (e < thr) {
+            q0 = __fadd_rn(q0, p0);
+            q1 = __fadd_rn(q1, p1);
+        }
+    }
+    return make_float2(__fsqrt_rn(__fdiv_rn(q0, fn)), __fsqrt_rn(__fdiv_rn(q1, fn)));
+}
+
+// Cursor over the (masked) error array: the next selected value, in index order.
+struct ErrCursor {
+    const float* v;
+    float thr;
+    bool masked;   // only the values below thr (the inliers); else every element
+    int i;
+    __device__ __forceinline__ float next() {
+        if (masked)
+            while (!(v[i] < thr)) ++i;
+        return v[i++];
+    }
+};
+
+// NumPy's pairwise_sum over the next n values of the cursor (numpy/core/src/umath/loops_utils.h.src): a block of
+// at most 128 values.
+__device__ __forceinline__ float np_pairwise_leaf_f32(ErrCursor& c, int n) {
+    if (n < 8) {
+        float res = 0.f;
+        for (int i = 0; i < n; ++i) res = __fadd_rn(res, c.next());
+        return res;
+    }
+    float r[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = c.next();
+    int i = 8;
+    for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) r[k] = __fadd_rn(r[k], c.next());
+    }
+    float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
+                          __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+    for (; i < n; ++i) res = __fadd_rn(res, c.next());
+    return res;
+}
+
+// ... and its recursion (n > 128: the halves split at a multiple of 8, left half first), with an explicit stack:
+// device threads have 1 KiB of call stack by default.
+__device__ __forceinline__ float np_pairwise_f32(ErrCursor& c, int n) {   // inlined: the cursor stays in registers
+    constexpr int kDepth = 28;   // n halves every level
+    int ns[kDepth];
+    float left[kDepth];
+    unsigned char stage[kDepth];
+    int sp = 0;
+    ns[0] = n;
+    stage[0] = 0;
+    float ret = 0.f;
+    while (true) {
+        if (stage[sp] == 0) {
+            if (ns[sp] <= 128) {
+                ret = np_pairwise_leaf_f32(c, ns[sp]);
+                if (--sp < 0) break;
+                continue;
+            }
+            int n2 = ns[sp] / 2;
+            n2 -= n2 % 8;
+            stage[sp] = 1;
+            ns[sp + 1] = n2;
+            stage[sp + 1] = 0;
+            ++sp;
+        } else if (stage[sp] == 1) {
+            left[sp] = ret;
+            int n2 = ns[sp] / 2;
+            n2 -= n2 % 8;
+            stage[sp] = 2;
+            ns[sp + 1] = ns[sp] - n2;
+            stage[sp + 1] = 0;
+            ++sp;
+        } else {
+            ret = __fadd_rn(left[sp], ret);
+            if (--sp < 0) break;
+        }
+    }
+    return ret;
+}
+
+// np.mean of the selected errors (float32 sum / count).
+__device__ __noinline__ float np_mean_f32(const float* v, float thr, bool masked, int n_sel) {
+    ErrCursor c{v, thr, masked, 0};
+    return __fdiv_rn(np_pairwise_f32(c, n_sel), static_cast<float>(n_sel));
 }
 
 __device__ __forceinline__ float4 load_match(const float* __restrict__ p1,
@@ -554,25 +674,54 @@ ransac_verify_kernel(int n_pairs, const long long* __restrict__ off, const int32
                 st[9] += static_cast<double>(q.z) * q.z; st[10] += static_cast<double>(q.w) * q.w;
             }
         }
-        block_sum<11>(st, sh);
+        block_sum<11>(st, sh);   // (its barriers also publish the error array to the whole block)
+        // The gates in float64 first.  NumPy's float32 results (sequential sums of <= n terms, pairwise for the means)
+        // lie within gate * (n + 5) * 2^-24 of these, so a pair is decided unless a quantity sits within
+        // gate * (n + 16) * 2^-22 of its gate; only such a BORDERLINE pair (rare) pays for the exact float32 walks.
+        const double n_in = st[0];
+        const int n_inl = static_cast<int>(n_in);
+        const double tol = (n_in + 16.0) * (1.0 / 4194304.0);
+        double sd64[4] = {0, 0, 0, 0};
+        bool border = false;
+        if (n_inl > 0) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const double mean = st[3 + k] / n_in;
+                double var = st[7 + k] / n_in - mean * mean;
+                var = var > 0 ? var : 0;
+                sd64[k] = sqrt(var);
+                border = border || fabs(sd64[k] - prm.min_spread) <= prm.min_spread * tol;
+            }
+            border = border || fabs(st[2] / n_in - prm.max_error) <= prm.max_error * tol;
+        }
+        if (border) {   // block-uniform: every thread holds the same sums
+            const int task = (threadIdx.x & 31) == 0 ? static_cast<int>(threadIdx.x >> 5) : -1;
+            const float* ev = sym + base;
+            if (task == 0 || task == 1) {
+                const float2 sd = np_std2_f32(task == 0 ? p1 : p2, 2, ev, vthr, m, n_inl);
+                sh.np_res[2 * task] = sd.x;
+                sh.np_res[2 * task + 1] = sd.y;
+            } else if (task == 2) {
+                sh.np_res[4] = np_mean_f32(ev, vthr, true, n_inl);
+            } else if (task == 3) {
+                sh.np_res[5] = np_mean_f32(ev, vthr, false, m);
+            }
+            __syncthreads();
+        }
         if (threadIdx.x == 0) {
-            const double n_in = st[0];
             sfm_pair_metrics mt;
             mt.total_matches = m;
-            mt.inliers = static_cast<int>(n_in);
+            mt.inliers = n_inl;
             const double ratio = m > 0 ? n_in / m : 0.0;
             mt.inlier_ratio = static_cast<float>(ratio);
-            mt.reprojection_error = n_in > 0 ? static_cast<float>(st[2] / n_in) : __int_as_float(0x7f800000);
-            mt.symmetric_error = m > 0 ? static_cast<float>(st[1] / m) : 0.f;
-            bool spread = n_in > 0;
+            mt.reprojection_error = n_inl > 0 ? (border ? sh.np_res[4] : static_cast<float>(st[2] / n_in))
+                                              : __int_as_float(0x7f800000);
+            mt.symmetric_error = m > 0 ? (border ? sh.np_res[5] : static_cast<float>(st[1] / m)) : 0.f;
+            bool spread = n_inl > 0;
             if (spread) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const double mean = st[3 + k] / n_in;
-                    double var = st[7 + k] / n_in - mean * mean;
-                    var = var > 0 ? var : 0;
-                    spread = spread && (static_cast<float>(sqrt(var)) > static_cast<float>(prm.min_spread));
-                }
+                for (int k = 0; k < 4; ++k)
+                    spread = spread && ((border ? sh.np_res[k] : static_cast<float>(sd64[k])) > static_cast<float>(prm.min_spread));
             }
             mt.well_distributed = spread ? 1 : 0;
             mt.ransac_inliers = ransac_inl;

@@ -31,7 +31,7 @@ def _dev(a, dtype):
 
 
 def test_verification_given_reference_F(ctx, bunny):
-    """Same F in -> identical inlier masks, metrics within 1e-4, same gate decision
+    """Same F in -> identical inlier masks, metrics within 2e-6, same gate decision
     (reference utils/find_matches.py:157-214 on all 148 shipped pairs)."""
     from sfm_b200 import lib as L
     z = bunny
@@ -48,10 +48,74 @@ def test_verification_given_reference_F(ctx, bunny):
     g = z["metrics"]
     assert np.array_equal(met["inliers"], g[:, 0].astype(np.int32))
     assert np.array_equal(met["total_matches"], np.diff(off).astype(np.int32))
-    assert np.allclose(met["reprojection_error"], g[:, 2], rtol=1e-4, atol=0)
-    assert np.allclose(met["symmetric_error"], g[:, 3], rtol=1e-4, atol=0)
+    # float64 sums rounded once (NumPy's float32 sums only for pairs within rounding of a gate): a few ulp
+    assert np.allclose(met["reprojection_error"], g[:, 2], rtol=2e-6, atol=0)
+    assert np.allclose(met["symmetric_error"], g[:, 3], rtol=2e-6, atol=0)
     assert np.array_equal(met["well_distributed"].astype(bool), g[:, 4].astype(bool))
     assert np.array_equal(status == L.PAIR_OK, z["passed"])
+
+
+def test_gate_quantities_in_numpy_float32(ctx):
+    """verify_match_quality's gates read np.std(pts[inlier_mask], axis=0) > 20 and np.mean(sym[inlier_mask]) <= 2
+    on float32 arrays (reference utils/find_matches.py:176-186, :203-214).  Pairs built to sit within float32
+    rounding of the 20 px spread gate -- the kernel then walks the pair in NumPy's own float32 order
+    (csrc/ransac.cu: np_std2_f32, np_pairwise_f32): its decision must be NumPy's float32 one (an f64 restatement
+    flips some of them), and both error means must equal np.mean bit for bit, for match counts on either side of
+    NumPy's pairwise-summation block sizes (8, 128, splits at multiples of 8)."""
+    from sfm_b200 import lib as L
+    rng = np.random.default_rng(2024)
+    counts = [1, 2, 7, 8, 9, 15, 16, 17, 127, 128, 129, 136, 255, 256, 257, 263, 1000, 2049, 4100] + \
+        [int(c) for c in rng.integers(20, 700, 1500)]
+    pts1, pts2 = [], []
+    for n in counts:
+        y = rng.normal(384, 120, n)
+        x = rng.normal(0, 1, n)
+        # epipolar lines y' = y: the vertical offset IS the point-line distance in both images
+        dy = rng.choice([0.0, 0.5, 1.25, 2.5, 3.5, 6.0], n, p=[0.2, 0.3, 0.2, 0.15, 0.1, 0.05])
+        inl = dy < 3.0
+        # x spread OF THE INLIERS within ~1e-6 relative of the gate; every coordinate a float32 value
+        sd = x[inl].std() if inl.sum() > 1 else 0.0
+        x = 512 + x / sd * 20.0 * (1 + rng.uniform(-2e-6, 2e-6)) if sd > 0 else np.full(n, 512.0)
+        a = np.stack([x, y], 1).astype(np.float32)
+        b = a + np.stack([rng.normal(40, 25, n), dy], 1).astype(np.float32)
+        pts1.append(a)
+        pts2.append(b.astype(np.float32))
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    p1, p2 = np.concatenate(pts1), np.concatenate(pts2)
+    F = np.tile(np.array([0, 0, 0, 0, 0, -1, 0, 1, 0], np.float64), (len(counts), 1))
+    o = ctx.verify_given_F(off, _dev(p1, torch.float32), _dev(p2, torch.float32), _dev(F, torch.float64))
+    torch.cuda.synchronize()
+    mask = o["mask"].cpu().numpy().astype(bool)
+    sym = o["sym"].cpu().numpy()
+    met = L.metrics_to_numpy(o["metrics"])
+    status = o["status"].cpu().numpy()
+    n_f64_differs = n_border = 0
+    for k, n in enumerate(counts):
+        s = slice(int(off[k]), int(off[k + 1]))
+        m, e = mask[s], sym[s]
+        assert met["inliers"][k] == m.sum()
+        if not m.any():
+            assert not met["well_distributed"][k] and np.isinf(met["reprojection_error"][k])
+            assert np.isclose(met["symmetric_error"][k], np.mean(e), rtol=2e-6)
+            continue
+        # the kernel's own rule for "within rounding of a gate" (then it walks in NumPy's float32 order)
+        sd64 = np.concatenate([np.std(p1[s][m].astype(np.float64), axis=0), np.std(p2[s][m].astype(np.float64), axis=0)])
+        tol = (m.sum() + 16) * 2.0 ** -22
+        border = bool(np.any(np.abs(sd64 - 20) <= 20 * tol) or abs(np.mean(e[m].astype(np.float64)) - 2.0) <= 2.0 * tol)
+        n_border += border
+        if border:
+            assert met["symmetric_error"][k] == np.mean(e), (k, n)
+            assert met["reprojection_error"][k] == np.mean(e[m]), (k, n)
+        else:
+            assert np.isclose(met["symmetric_error"][k], np.mean(e), rtol=2e-6)
+            assert np.isclose(met["reprojection_error"][k], np.mean(e[m]), rtol=2e-6)
+        sd = np.concatenate([np.std(p1[s][m], axis=0), np.std(p2[s][m], axis=0)])        # float32, as the reference
+        want = bool(np.all(sd > 20))
+        assert bool(met["well_distributed"][k]) == want, (k, n, sd)
+        n_f64_differs += bool(np.all(sd64.astype(np.float32) > 20)) != want
+        passed = (m.sum() >= 15) and (m.mean() >= 0.3) and (np.mean(e[m]) <= 2.0) and want
+        assert (status[k] == L.PAIR_OK) == passed, (k, n)
+    assert n_f64_differs > 0 and n_border > 1000      # the set really straddles the gate at float32 resolution
 
 
 def _ransac(ctx, z, **kw):
